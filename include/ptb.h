@@ -1,0 +1,181 @@
+/* ptb.h — C ABI of the B200-native render backend (libptb.so).
+ *
+ * The reference (CouncilmanJeremyJamm/path_tracer) has no FFI or plugin interface: its seam is the Rust
+ * closure body src/main.rs:186-207 and the types that feed it.  This header is what a `ffi.rs` for that
+ * seam would bind: plain pointers and sizes, no C++/torch types, `int` status codes,
+ * never unwinds.  Each entry point cites the reference interface it replaces.
+ *
+ * Ownership: the caller owns every host array (borrowed for the duration of the call; the library copies to
+ * the device).  The library owns all device memory and frees it in ptb_destroy.  Output host buffers are
+ * caller-allocated.  Image arrays are row-major with row 0 = bottom row (camera.rs:96, shader.wgsl:44-49).
+ *
+ * Threading: one context per GPU; calls on one context must be externally serialised (the reference calls
+ * the seam once per frame from the main thread, main.rs:179-219); different contexts may be driven from
+ * different threads.  Kernels run on a per-context stream; ptb_render is asynchronous, ptb_read_* and
+ * ptb_synchronize wait for it.
+ *
+ * There is no CPU fallback: every compute entry point returns PTB_ERR_NO_DEVICE without a CUDA device.
+ */
+#ifndef PTB_H
+#define PTB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PTB_ABI_VERSION 1
+
+typedef struct ptb_context ptb_context;
+
+enum ptb_status
+{
+    PTB_OK = 0,
+    PTB_ERR_INVALID = 1,     /* bad argument / scene the reference would reject (panics upstream, e.g. model.rs:43, tlas_bvh.rs:58) */
+    PTB_ERR_CUDA = 2,        /* CUDA runtime error, see ptb_last_error */
+    PTB_ERR_NO_DEVICE = 3,   /* no CUDA device / wrong architecture */
+    PTB_ERR_OOM = 4,
+    PTB_ERR_NOT_BUILT = 5,   /* scene not uploaded / ptb_build not called */
+    PTB_ERR_UNSUPPORTED = 6  /* valid upstream but beyond a documented limit of this backend (e.g. > 64 media) */
+};
+
+/* Material kinds: enum Material, material.rs:80-89 (GGX split by GGXModel, material.rs:171-180). */
+enum ptb_material_kind
+{
+    PTB_LAMBERTIAN = 0,     /* Lambertian::new(albedo)                      material.rs:99  */
+    PTB_EMISSIVE = 1,       /* Emissive::new(emitted)                       material.rs:126 */
+    PTB_SPECULAR = 2,       /* Specular::new(colour)                        material.rs:146 */
+    PTB_GGX_METAL = 3,      /* GGX::new_metal(colour, roughness)            material.rs:290 */
+    PTB_GGX_DIELECTRIC = 4, /* GGX::new_dielectric(colour, roughness, ior, volume) material.rs:305 */
+    PTB_DIELECTRIC = 5      /* Dielectric::new(colour, ior, volume)         material.rs:475 */
+};
+
+typedef struct ptb_material
+{
+    uint32_t kind;
+    float colour[3];         /* albedo | emitted | colour */
+    float roughness;         /* linear roughness; the library applies powi(2).clamp(1e-4, 0.9999) as material.rs:294 */
+    float ior;
+    uint32_t has_volume;     /* Option<Volume>; honoured for the two transmissive kinds only */
+    float vol_absorption[3]; /* Volume::new(absorption, k, c, g), volume.rs:136 */
+    float vol_k, vol_c, vol_g;
+} ptb_material;
+
+/* One `Model` (model.rs:27-33) = one BLAS: a triangle range of the vertex array + one material (blas.rs:164-170). */
+typedef struct ptb_blas_desc
+{
+    uint32_t first_tri, tri_count;
+    ptb_material material;
+} ptb_blas_desc;
+
+/* One entry of `Model.matrices`: glam Affine3A column-major (x_axis, y_axis, z_axis, translation).
+ * Instances must be grouped in BLAS order (the order `for info in blas_info { for matrix in ... }` of tlas_bvh.rs:90-104). */
+typedef struct ptb_instance
+{
+    uint32_t blas;
+    float affine[12];
+} ptb_instance;
+
+/* ---- context ------------------------------------------------------------------------------------------ */
+int ptb_abi_version(void);
+int ptb_create(int device_ordinal, ptb_context** out);
+void ptb_destroy(ptb_context* ctx);
+/* Message for the last non-OK status on this context (ctx == NULL: last failure of ptb_create on this thread).
+ * Valid until the next call on the context. */
+const char* ptb_last_error(const ptb_context* ctx);
+int ptb_synchronize(ptb_context* ctx);
+
+/* ---- Scene::new(Vec<Model>)  scene.rs:21-35 --------------------------------------------------------------
+ * verts: ntri * 3 * 6 floats, per vertex (position xyz, normal xyz) = `Vertex` (model.rs:13-18), three per
+ * triangle in the order load_obj emits them (blas.rs:97-119).  Validates what the reference asserts or panics
+ * on: non-empty BLASes, unit-scale matrices (model.rs:42-43), at least one emissive model (scene.rs:26 ->
+ * tlas_bvh.rs:58).  ptb_build runs BLAS::new / TLAS::new (bit-exact node order, blas_bvh.rs:62-136,
+ * tlas_bvh.rs:85-138), LightSampler::new (light_sampler.rs:41-61), derives the 8-wide device layout and uploads. */
+int ptb_scene_upload(ptb_context* ctx, const float* verts, uint64_t ntri, const ptb_blas_desc* blas, uint32_t nblas, const ptb_instance* inst, uint32_t ninst);
+/* Optional environment map, linear RGB, row-major w*h*3 (what ImageHelper::load_image yields, image_helper.rs:25-33);
+ * without it the background is the constant 0.006 of integrator.rs:265. */
+int ptb_scene_set_env(ptb_context* ctx, uint32_t w, uint32_t h, const float* rgb);
+int ptb_build(ptb_context* ctx);
+/* Host threads used by ptb_build (0 = hardware_concurrency). */
+int ptb_set_build_threads(ptb_context* ctx, int threads);
+
+/* ---- build output in reference arena order — for bit-exact comparison ------------------
+ * BLAS nodes (blas_bvh.rs:36-58): boxes 6 floats/node (min xyz, max xyz); meta 3 u32/node:
+ *   kind 0 Branch {left,right} | 1 LeafSingle {prim,0} | 2 Leaf {first index into leaf_prims, count}.
+ * triangles: 30 floats each: positions[9], normals[9], n0[4], n1[4], n2[4] (primitive.rs:14-27). */
+int ptb_bvh_blas_counts(ptb_context* ctx, uint32_t blas, uint32_t* node_count, uint32_t* leaf_prim_count, uint32_t* root);
+int ptb_bvh_blas_nodes(ptb_context* ctx, uint32_t blas, float* boxes6, uint32_t* meta3, uint32_t* leaf_prims);
+int ptb_bvh_blas_triangles(ptb_context* ctx, uint32_t blas, float* out30);
+/* TLAS nodes (tlas_bvh.rs:32-52), which = 0 world (scene.rs:25) | 1 lights (scene.rs:26): meta kind 0 Branch {left,right} |
+ * 1 Leaf {TLAS-local blas index, instance ordinal}; matrices 24 floats/node (matrix, inv_matrix; zero for branches);
+ * blas_ids: TLAS-local blas index -> scene blas index. */
+int ptb_bvh_tlas_counts(ptb_context* ctx, int which, uint32_t* node_count, uint32_t* root, uint32_t* nblas);
+int ptb_bvh_tlas_nodes(ptb_context* ctx, int which, float* boxes6, uint32_t* meta3, float* matrices24, uint32_t* blas_ids);
+/* LightSampler (light_sampler.rs:23-28): items 2 u32/light (lights-TLAS blas index, prim id), pdf, cdf, max. */
+int ptb_light_count(ptb_context* ctx, uint32_t* count);
+int ptb_light_sampler(ptb_context* ctx, uint32_t* items2, float* pdf, float* cdf, float* max);
+/* Wide-layout statistics: [0] wide nodes, [1] leaf headers, [2] triangle slots, [3] bytes of device BVH data,
+ * [4] max wide depth (TLAS+BLAS), [5] binary nodes, [6] instances, [7] device stack bound. */
+int ptb_bvh_stats(ptb_context* ctx, uint64_t out[8]);
+
+/* ---- fixed ray batches: TLAS::intersect (tlas.rs:66-110) / TLAS::any_intersect (tlas.rs:111-144) ---------------
+ * which: 0 = scene.world, 1 = scene.lights.  kernel: 0 = 8-wide persistent kernel (the renderer's), 1 = reference-order
+ * binary kernel (walks the reference's own binary BVH in the reference's visit order; bit-exact incl. ties).
+ * o3/d3: n*3 floats (d normalised, ray.rs:12), tmax: n floats.  Host pointers; copies happen inside the call.
+ * Outputs may be NULL except `hit`.  blas = scene blas index, inst = instance ordinal (`Model`x`matrices` order),
+ * normal = world-space ray-facing shading normal (primitive.rs:161-165, tlas.rs:103-105). */
+int ptb_trace_closest(ptb_context* ctx, int which, int kernel, uint64_t n, const float* o3, const float* d3, const float* tmax, uint8_t* hit, float* t, float* u,
+                      float* v, uint32_t* prim, uint32_t* blas, uint32_t* inst, uint8_t* front, float* normal3);
+int ptb_trace_any(ptb_context* ctx, int which, int kernel, uint64_t n, const float* o3, const float* d3, const float* tmax, uint8_t* hit);
+/* Same kernels on rays already resident in device memory (benchmarks): upload once, launch many times.
+ * ptb_trace_resident runs `repeats` launches and returns the mean device time per launch (CUDA events on the context stream). */
+int ptb_trace_upload(ptb_context* ctx, uint64_t n, const float* o3, const float* d3, const float* tmax);
+int ptb_trace_resident(ptb_context* ctx, int which, int kernel, int any_hit, int repeats, float* mean_ms);
+int ptb_trace_download(ptb_context* ctx, uint8_t* hit, float* t, uint32_t* prim, uint32_t* inst);
+
+/* ---- Camera::new / Camera::create_ray (camera.rs:17-31, 94-105); SobolSampler::get_ss_sobol (sampling.rs:97-114) ------ */
+int ptb_set_camera(ptb_context* ctx, const float origin[3], const float target[3], float fov_deg, float aspect_ratio);
+int ptb_camera_rays(ptb_context* ctx, uint64_t n, const float* st2, float* o3, float* d3);           /* runs the raygen device code */
+int ptb_ss_sobol(ptb_context* ctx, uint64_t n, const uint32_t* index, const uint32_t* seed, float* xy2); /* runs the raygen device code */
+int ptb_rng_stream(ptb_context* ctx, uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t n, uint32_t* out); /* device RNG probe */
+
+/* ---- the frame loop main.rs:181-207 + accumulate.wgsl:20-23 ------------------------------------------------------
+ * ptb_render traces samples [sample_begin, sample_begin+sample_count) of every pixel (one "frame" upstream = one sample per
+ * pixel) with integrate(ray, scene, env, rng, max_bounces) (integrator.rs:143-149) and adds (rgb, 1) per sample into the
+ * device accumulation buffer (created/zeroed by ptb_frame_begin; W*H float4).  RNG streams are keyed by (seed, pixel,
+ * global sample index) so disjoint sample ranges on different GPUs compose.  enable_nee = ENABLE_NEE (main.rs:51).
+ * ptb_read_accum: sum of samples in rgb, sample count in w — the accumulation texture of state.rs:583; display = rgb / w
+ * (shader.wgsl:63).  ptb_read_aux: `position` (first-hit point, t) and `id` ((id << 16) | first blas id) of main.rs:204-206. */
+int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height);
+int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_bounces, int enable_nee);
+int ptb_read_accum(ptb_context* ctx, float* rgba);
+int ptb_read_aux(ptb_context* ctx, float* position4, uint32_t* id);
+/* Optional second moment (sum of squared sample values) for statistical parity tests; must be enabled before ptb_frame_begin. */
+int ptb_enable_second_moment(ptb_context* ctx, int enable);
+int ptb_read_second_moment(ptb_context* ctx, float* rgba);
+/* Device pointer of the accumulation buffer (W*H*4 floats) for an external collective (NCCL reduce over NVLink), and an
+ * in-place `+=` from another device buffer of the same shape (used after a gather-style exchange). */
+int ptb_accum_device_ptr(ptb_context* ctx, void** dptr, size_t* bytes);
+/* Use caller-owned device memory (e.g. a torch tensor) as accumulation buffer; NULL reverts to the internal one. */
+int ptb_bind_accum(ptb_context* ctx, void* dptr, size_t bytes);
+
+/* ---- counters & timing -------------------------------------------------------------------------------------------
+ * counters since the last ptb_reset_counters: [0] extend rays (world closest-hit), [1] shadow rays (world any-hit),
+ * [2] light probes (lights-TLAS closest-hit), [3] paths (camera samples), [4] wavefront iterations, [5] kernel launches,
+ * [6] primary rays, [7] reserved. */
+int ptb_get_counters(ptb_context* ctx, uint64_t out[8]);
+int ptb_reset_counters(ptb_context* ctx);
+/* With profiling on, every kernel launch of ptb_render is bracketed by CUDA events on the context stream.
+ * times_ms: [0] whole ptb_render call (always measured), [1] raygen/regenerate, [2] extend, [3] shade, [4] shadow,
+ * [5] light probe, [6] accumulate/finalise, [7] queue bookkeeping; launches: same indices. */
+int ptb_set_profiling(ptb_context* ctx, int enable);
+int ptb_get_timing(ptb_context* ctx, float times_ms[8], uint32_t launches[8]);
+/* Tunables (evidence switches for DESIGN.md's layout decisions): name in {"sort_materials","extend_kernel","block_threads","blocks_per_sm"}. */
+int ptb_set_option(ptb_context* ctx, const char* name, int value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTB_H */

@@ -1,0 +1,128 @@
+// context.h — internal state behind the opaque ptb_context of include/ptb.h.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "host_scene.h"
+
+namespace ptb {
+
+template <class T>
+struct DBuf  // owning device array
+{
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t resize(size_t count)
+    {
+        if (count <= n && p) return cudaSuccess;
+        release();
+        if (count == 0) return cudaSuccess;
+        cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+        if (e == cudaSuccess) n = count;
+        else p = nullptr;
+        return e;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+    size_t bytes() const { return n * sizeof(T); }
+};
+
+// SoA wavefront state of the renderer (render.cu); one slot per pixel (path regeneration keeps a slot on its pixel, so
+// per-pixel accumulation needs no atomics).
+struct RenderState;
+
+}  // namespace ptb
+
+struct ptb_context
+{
+    int device = -1;
+    bool host_only = false;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    int build_threads = 0;
+
+    ptb::HostScene scene;
+    // device copies of the layout
+    ptb::DBuf<uint4> d_wide;
+    ptb::DBuf<float4> d_leaf_headers, d_tri_planes, d_planes_by_prim;
+    ptb::DBuf<uint32_t> d_tri_prim, d_leaf_prims;
+    ptb::DBuf<ptb::BinNode> d_bin;
+    ptb::DBuf<float> d_tri_normals, d_tri_positions, d_env;
+    ptb::DBuf<ptb::InstanceRow> d_inst;
+    ptb::DBuf<ptb::MaterialRow> d_mat;
+    ptb::DBuf<ptb::VolumeRow> d_vol;
+    ptb::DBuf<ptb::LightRow> d_lights;
+    ptb::SceneDev S{};
+    bool device_ready = false;
+    uint64_t device_bvh_bytes = 0;
+
+    // resident ray batch (ptb_trace_upload / ptb_trace_resident)
+    ptb::DBuf<float> t_o, t_d, t_tmax, t_t, t_u, t_v, t_normal;
+    ptb::DBuf<uint32_t> t_prim, t_blas, t_inst;
+    ptb::DBuf<uint8_t> t_hit, t_front;
+    ptb::DBuf<unsigned long long> t_counter;
+    uint64_t t_n = 0;
+
+    // camera (Camera::new): ray matrix = matrix * inv_projection (column-major 4x4) and eye
+    float cam_m[16] = {0};
+    float cam_eye[3] = {0};
+    bool cam_set = false;
+
+    // options
+    int opt_sort_materials = 1;
+    int opt_extend_kernel = 0;  // 0 wide, 1 reference-order
+    int opt_block_threads = 128;
+    int opt_blocks_per_sm = 8;
+    int profiling = 0;
+    int second_moment = 0;
+
+    ptb::RenderState* rs = nullptr;
+
+    int fail(int code, const std::string& m)
+    {
+        err = m;
+        return code;
+    }
+    int cuda_fail(cudaError_t e, const char* where)
+    {
+        err = std::string(where) + ": " + cudaGetErrorString(e);
+        return e == cudaErrorMemoryAllocation ? PTB_ERR_OOM : PTB_ERR_CUDA;
+    }
+};
+
+#define PTB_CUDA(ctx, call)                                         \
+    do                                                              \
+    {                                                               \
+        cudaError_t _e = (call);                                    \
+        if (_e != cudaSuccess) return (ctx)->cuda_fail(_e, #call);  \
+    } while (0)
+
+namespace ptb {
+// render.cu
+void render_state_destroy(ptb_context* ctx);
+// trace kernels (kernels_trace.cu)
+struct TraceArgs
+{
+    const float* o;
+    const float* d;
+    const float* tmax;
+    uint8_t* hit;
+    float* t;
+    float* u;
+    float* v;
+    uint32_t* prim;
+    uint32_t* blas;
+    uint32_t* inst;
+    uint8_t* front;
+    float* normal;
+    unsigned long long* counter;
+};
+cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream);
+}  // namespace ptb

@@ -1,0 +1,416 @@
+// traverse.h — per-ray traversal, host+device (the device kernels in kernels_*.cu wrap these; tests/hostemu compiles the
+// very same functions for the CPU so the logic can be unit-tested without a GPU — that harness is test-only and is
+// never linked into libptb.so).
+//
+//  * wide_closest / wide_any   : TLAS::intersect / TLAS::any_intersect (tlas.rs:66-144) over the 8-wide layout.
+//  * bin_closest / bin_any     : the same two functions walking the reference's own binary trees in the reference's
+//                                visit order (push_to_stack, blas.rs:133-162) — bit-exact including ties.
+//
+// Exactness argument for the wide kernels: a triangle's (t,u,v) is a pure function of the BLAS-space ray,
+// the triangle planes and the entry distance of the *reference leaf box* (primitive.rs:147-155, boundingbox.rs:129), all
+// of which are evaluated here with the reference's operation order (exact_math.h).  Quantised child boxes only cull;
+// they are conservative by construction (host_wide.cpp) plus an explicit rounding slack below, and slab results are
+// monotone under box inclusion, so every leaf the reference can reach with a hit is reached here.  The winner is the
+// minimum t; only exact ties may resolve differently (the reference keeps the last-visited of equal hits).
+#pragma once
+#include "exact_math.h"
+#include "layout.h"
+
+namespace ptb {
+
+using ex::V3;
+
+#if defined(__CUDA_ARCH__)
+#define PTB_LDG4U(p) __ldg(p)
+#define PTB_LDG4F(p) __ldg(p)
+#define PTB_LDGU(p) __ldg(p)
+#define PTB_LDGF(p) __ldg(p)
+#else
+#define PTB_LDG4U(p) (*(p))
+#define PTB_LDG4F(p) (*(p))
+#define PTB_LDGU(p) (*(p))
+#define PTB_LDGF(p) (*(p))
+#endif
+
+struct Hit
+{
+    float t, u, v;
+    uint32_t slot_or_prim;  // wide: triangle slot; bin: BLAS-local prim id (resolved to prim id by finish_hit)
+    uint32_t inst;          // InstanceRow index, 0xffffffff = miss
+};
+
+struct TravRay
+{
+    V3 o, d;     // current space (world or BLAS)
+    V3 inv;      // exact 1/d (ray.rs:16), may be +-inf
+    V3 idq;      // finite reciprocal for the conservative quantised tests
+    uint32_t oi; // 7 ^ octant
+};
+
+PTB_HD float finite_recip(float d)
+{
+    const float tiny = 8.6736174e-19f;  // 2^-60
+    float a = fabsf(d) < tiny ? copysignf(tiny, d) : d;
+    return 1.0f / a;
+}
+PTB_HD void set_ray(TravRay& r, V3 o, V3 d)
+{
+    r.o = o;
+    r.d = d;
+    r.inv = ex::recip(d);
+    r.idq = ex::v3(finite_recip(d.x), finite_recip(d.y), finite_recip(d.z));
+    uint32_t oct = (d.x < 0.0f ? 4u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 1u : 0u);
+    r.oi = 7u ^ oct;
+}
+// Ray::transform (ray.rs:22-28)
+PTB_HD void transform_ray(TravRay& out, V3 o, V3 d, const float* inv12)
+{
+    V3 c0 = ex::v3(inv12[0], inv12[1], inv12[2]), c1 = ex::v3(inv12[3], inv12[4], inv12[5]), c2 = ex::v3(inv12[6], inv12[7], inv12[8]);
+    V3 t = ex::v3(inv12[9], inv12[10], inv12[11]);
+    set_ray(out, ex::add(ex::m3_mul(c0, c1, c2, o), t), ex::m3_mul(c0, c1, c2, d));
+}
+
+PTB_HD float qbyte(uint32_t w, int k) { return (float)((w >> (8 * k)) & 0xffu); }
+
+// XOR-permute two packed 8-bit masks (bits 0..7 and 8..15): bit (s ^ x) of the result = bit s of the input
+PTB_HD uint32_t xor_permute16(uint32_t m, uint32_t x)
+{
+    if (x & 1u) m = ((m & 0x5555u) << 1) | ((m >> 1) & 0x5555u);
+    if (x & 2u) m = ((m & 0x3333u) << 2) | ((m >> 2) & 0x3333u);
+    if (x & 4u) m = ((m & 0x0f0fu) << 4) | ((m >> 4) & 0x0f0fu);
+    return m;
+}
+
+// Conservative test of the 8 quantised child boxes of one node; returns the hit mask by slot.
+PTB_HD uint32_t wide_node_test(const uint4& q0, const uint4& q2, const uint4& q3, const uint4& q4, const TravRay& r, float t_max)
+{
+    const float px = ex::from_bits(q0.x), py = ex::from_bits(q0.y), pz = ex::from_bits(q0.z);
+    const float sx0 = ex::from_bits((q0.w & 0xffu) << 23), sy0 = ex::from_bits(((q0.w >> 8) & 0xffu) << 23), sz0 = ex::from_bits(((q0.w >> 16) & 0xffu) << 23);
+    const float sx = sx0 * r.idq.x, sy = sy0 * r.idq.y, sz = sz0 * r.idq.z;
+    const float bx = (px - r.o.x) * r.idq.x, by = (py - r.o.y) * r.idq.y, bz = (pz - r.o.z) * r.idq.z;
+    // rounding slack: the fused evaluation below differs from the exact slab arithmetic by a few ulps of |b| + 255|s|
+    const float k = 9.5367432e-7f;  // 2^-20
+    const float ex_ = (fabsf(bx) + 255.0f * fabsf(sx)) * k, ey_ = (fabsf(by) + 255.0f * fabsf(sy)) * k, ez_ = (fabsf(bz) + 255.0f * fabsf(sz)) * k;
+    const float bnx = bx - ex_, bfx = bx + ex_, bny = by - ey_, bfy = by + ey_, bnz = bz - ez_, bfz = bz + ez_;
+    // near/far byte planes by direction sign
+    const bool nx = r.idq.x < 0.0f, ny = r.idq.y < 0.0f, nz = r.idq.z < 0.0f;
+    const uint32_t lox0 = q2.x, lox1 = q2.y, loy0 = q2.z, loy1 = q2.w, loz0 = q3.x, loz1 = q3.y;
+    const uint32_t hix0 = q3.z, hix1 = q3.w, hiy0 = q4.x, hiy1 = q4.y, hiz0 = q4.z, hiz1 = q4.w;
+    const uint32_t nx0 = nx ? hix0 : lox0, nx1 = nx ? hix1 : lox1, fx0 = nx ? lox0 : hix0, fx1 = nx ? lox1 : hix1;
+    const uint32_t ny0 = ny ? hiy0 : loy0, ny1 = ny ? hiy1 : loy1, fy0 = ny ? loy0 : hiy0, fy1 = ny ? loy1 : hiy1;
+    const uint32_t nz0 = nz ? hiz0 : loz0, nz1 = nz ? hiz1 : loz1, fz0 = nz ? loz0 : hiz0, fz1 = nz ? loz1 : hiz1;
+    uint32_t mask = 0;
+#pragma unroll
+    for (int s = 0; s < 8; ++s)
+    {
+        const int kb = s & 3;
+        const uint32_t wnx = s < 4 ? nx0 : nx1, wfx = s < 4 ? fx0 : fx1, wny = s < 4 ? ny0 : ny1, wfy = s < 4 ? fy0 : fy1, wnz = s < 4 ? nz0 : nz1, wfz = s < 4 ? fz0 : fz1;
+        // an empty slot has lo=255 > hi=0 on every axis: whichever is "near" the interval is empty for any direction
+        const uint32_t lo_b = ((s < 4 ? lox0 : lox1) >> (8 * kb)) & 0xffu, hi_b = ((s < 4 ? hix0 : hix1) >> (8 * kb)) & 0xffu;
+        const float tnx = fmaf(qbyte(wnx, kb), sx, bnx), tfx = fmaf(qbyte(wfx, kb), sx, bfx);
+        const float tny = fmaf(qbyte(wny, kb), sy, bny), tfy = fmaf(qbyte(wfy, kb), sy, bfy);
+        const float tnz = fmaf(qbyte(wnz, kb), sz, bnz), tfz = fmaf(qbyte(wfz, kb), sz, bfz);
+        const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, ex::EPS));
+        const float tf = fminf(fminf(tfx, tfy), fminf(tfz, t_max));
+        if (tn <= tf && lo_b <= hi_b) mask |= (1u << s);
+    }
+    return mask;
+}
+
+// hit record resolution shared by the kernels: normal, front-facing (primitive.rs:158-165, tlas.rs:103-105)
+PTB_HD void finish_hit(const SceneDev& S, V3 d_world, uint32_t inst, uint32_t prim, float u, float v, V3* normal, bool* front)
+{
+    const InstanceRow& R = S.inst[inst];
+    const float* nn = S.tri_normals + (size_t)(R.tri_base + prim) * 9;
+    V3 n = ex::tri_normal(ex::v3(PTB_LDGF(nn + 0), PTB_LDGF(nn + 1), PTB_LDGF(nn + 2)), ex::v3(PTB_LDGF(nn + 3), PTB_LDGF(nn + 4), PTB_LDGF(nn + 5)),
+                          ex::v3(PTB_LDGF(nn + 6), PTB_LDGF(nn + 7), PTB_LDGF(nn + 8)), u, v);
+    // BLAS-space direction = inv_matrix3 * d (Ray::transform)
+    V3 dl = ex::m3_mul(ex::v3(R.inv[0], R.inv[1], R.inv[2]), ex::v3(R.inv[3], R.inv[4], R.inv[5]), ex::v3(R.inv[6], R.inv[7], R.inv[8]), d_world);
+    bool ff = ex::dot3(dl, n) < 0.0f;
+    if (!ff) n = ex::neg(n);
+    *normal = ex::m3_mul(ex::v3(R.fwd[0], R.fwd[1], R.fwd[2]), ex::v3(R.fwd[3], R.fwd[4], R.fwd[5]), ex::v3(R.fwd[6], R.fwd[7], R.fwd[8]), n);
+    *front = ff;
+}
+
+// ------------------------------------------------------------------------------------------------------------------------
+// 8-wide traversal.  Stack entries (uint2): x = child_base | leaf header index, y = kind/payload:
+//   group   : y = hits_permuted (bits 0..7) | imask << 8            (bit 31 clear)
+//   instance: y = 0x80000000                                          x = leaf header index of a TLAS leaf
+// ------------------------------------------------------------------------------------------------------------------------
+template <bool ANY>
+PTB_HD bool wide_traverse(const SceneDev& S, int which, V3 o_world, V3 d_world, float t_max, Hit* hit)
+{
+    uint2 stack[WIDE_STACK_CAP];
+    int sp = 0;
+    TravRay ray;
+    set_ray(ray, o_world, d_world);
+    bool in_blas = false;
+    int blas_sp = 0;
+    uint32_t cur_inst = 0xffffffffu;
+    uint32_t node = S.tlas[which].wide_root;
+    uint2 G;
+    G.x = 0;
+    G.y = 0;
+    bool found = false;
+    const uint32_t NONE = 0xffffffffu;
+    for (;;)
+    {
+        if (node != NONE)
+        {
+            const uint4* np = S.wide + (size_t)node * 5;
+            const uint4 q0 = PTB_LDG4U(np), q1 = PTB_LDG4U(np + 1), q2 = PTB_LDG4U(np + 2), q3 = PTB_LDG4U(np + 3), q4 = PTB_LDG4U(np + 4);
+            node = NONE;
+            const uint32_t hits = wide_node_test(q0, q2, q3, q4, ray, t_max);
+            const uint32_t imask = q0.w >> 24, lmask = q1.z & 0xffu;
+            const uint32_t perm = xor_permute16((hits & imask) | ((hits & lmask) << 8), ray.oi);
+            const uint32_t ih = perm & 0xffu;
+            uint32_t lh = (perm >> 8) & 0xffu;
+            if (ih) { G.x = q1.x; G.y = ih | (imask << 8); }
+            else G.y = 0;
+            if (in_blas)
+            {
+                // triangle leaves: front to back, right now
+                while (lh)
+                {
+#if defined(__CUDA_ARCH__)
+                    const int p = 31 - __clz((int)lh);
+#else
+                    const int p = 31 - __builtin_clz(lh);
+#endif
+                    lh &= ~(1u << p);
+                    const uint32_t s = (uint32_t)p ^ ray.oi;
+#if defined(__CUDA_ARCH__)
+                    const uint32_t hidx = q1.y + __popc(lmask & ((1u << s) - 1u));
+#else
+                    const uint32_t hidx = q1.y + __builtin_popcount(lmask & ((1u << s) - 1u));
+#endif
+                    const float4 h0 = PTB_LDG4F(S.leaf_headers + (size_t)hidx * 2), h1 = PTB_LDG4F(S.leaf_headers + (size_t)hidx * 2 + 1);
+                    const uint32_t cw = ex::bits(h0.w);
+                    float t_enter = 0.0f;
+                    if (ANY || !(cw & LEAF_ROOT_FLAG))
+                    {
+                        // blas.rs:137-138 / :264 — exact reference leaf box, exact entry distance
+                        if (!ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), ray.o, ray.inv, t_max, &t_enter)) continue;
+                    }
+                    const uint32_t cnt = cw & ~LEAF_ROOT_FLAG, first = ex::bits(h1.w);
+                    for (uint32_t k = 0; k < cnt; ++k)
+                    {
+                        const float4* pp = S.tri_planes + (size_t)(first + k) * 3;
+                        const float4 a = PTB_LDG4F(pp), b = PTB_LDG4F(pp + 1), c = PTB_LDG4F(pp + 2);
+                        const float n0[4] = {a.x, a.y, a.z, a.w}, n1[4] = {b.x, b.y, b.z, b.w}, n2[4] = {c.x, c.y, c.z, c.w};
+                        if (ANY)
+                        {
+                            if (ex::tri_hit_bool(n0, n1, n2, ray.o, ray.d, t_max, t_enter)) return true;
+                        }
+                        else
+                        {
+                            float t, u, v;
+                            if (ex::tri_hit(n0, n1, n2, ray.o, ray.d, t_max, t_enter, &t, &u, &v))
+                            {
+                                t_max = t;
+                                hit->t = t; hit->u = u; hit->v = v; hit->slot_or_prim = first + k; hit->inst = cur_inst;
+                                found = true;
+                            }
+                        }
+                    }
+                }
+            }
+            else
+            {
+                // TLAS leaves: push the inner group first, then the instances far to near (nearest popped first)
+                if (G.y) { stack[sp++] = G; G.y = 0; }
+                uint32_t m = lh;
+                while (m)
+                {
+#if defined(__CUDA_ARCH__)
+                    const int p = __ffs((int)m) - 1;
+#else
+                    const int p = __builtin_ctz(m);
+#endif
+                    m &= m - 1;
+                    const uint32_t s = (uint32_t)p ^ ray.oi;
+#if defined(__CUDA_ARCH__)
+                    const uint32_t hidx = q1.y + __popc(lmask & ((1u << s) - 1u));
+#else
+                    const uint32_t hidx = q1.y + __builtin_popcount(lmask & ((1u << s) - 1u));
+#endif
+                    uint2 e;
+                    e.x = hidx;
+                    e.y = 0x80000000u;
+                    stack[sp++] = e;
+                }
+            }
+        }
+        if (G.y)
+        {
+            // descend into the nearest remaining child of the current group
+            const uint32_t ih = G.y & 0xffu, imask = (G.y >> 8) & 0xffu;
+#if defined(__CUDA_ARCH__)
+            const int p = 31 - __clz((int)ih);
+#else
+            const int p = 31 - __builtin_clz(ih);
+#endif
+            const uint32_t s = (uint32_t)p ^ ray.oi;
+#if defined(__CUDA_ARCH__)
+            node = G.x + __popc(imask & ((1u << s) - 1u));
+#else
+            node = G.x + __builtin_popcount(imask & ((1u << s) - 1u));
+#endif
+            G.y &= ~(1u << p);
+            if (G.y & 0xffu) stack[sp++] = G;
+            G.y = 0;
+            continue;
+        }
+        // current group exhausted
+        if (in_blas && sp == blas_sp)
+        {
+            in_blas = false;  // leave the instance: back to the world ray
+            set_ray(ray, o_world, d_world);
+        }
+        if (sp == 0) break;
+        const uint2 e = stack[--sp];
+        if (e.y & 0x80000000u)
+        {
+            // TLAS leaf (tlas.rs:88-100 / :132-139): exact leaf box with the current t_max, then Ray::transform
+            const float4 h0 = PTB_LDG4F(S.leaf_headers + (size_t)e.x * 2), h1 = PTB_LDG4F(S.leaf_headers + (size_t)e.x * 2 + 1);
+            float t_enter;
+            if (!ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), ray.o, ray.inv, t_max, &t_enter)) continue;
+            cur_inst = ex::bits(h1.w);
+            const InstanceRow& R = S.inst[cur_inst];
+            float inv12[12];
+#pragma unroll
+            for (int k = 0; k < 12; ++k) inv12[k] = PTB_LDGF(R.inv + k);
+            transform_ray(ray, o_world, d_world, inv12);
+            in_blas = true;
+            blas_sp = sp;
+            node = PTB_LDGU(&R.wide_root);
+        }
+        else G = e;
+    }
+    return found;
+}
+
+// ------------------------------------------------------------------------------------------------------------------------
+// Reference-order traversal over the binary trees (BinNode): a literal walk of tlas.rs:66-144 / blas.rs:214-294.
+// ------------------------------------------------------------------------------------------------------------------------
+struct BinEntry
+{
+    uint32_t id;
+    float t;
+};
+
+PTB_HD void bin_push2(const BinNode* nodes, uint32_t base, uint32_t l, uint32_t r, const TravRay& ray, float t_max, BinEntry* st, int& sp)  // blas.rs:133-162
+{
+    const BinNode& L = nodes[base + l];
+    const BinNode& Rn = nodes[base + r];
+    float tl, tr;
+    const bool hl = ex::slab(ex::v3(PTB_LDGF(&L.lo[0]), PTB_LDGF(&L.lo[1]), PTB_LDGF(&L.lo[2])), ex::v3(PTB_LDGF(&L.hi[0]), PTB_LDGF(&L.hi[1]), PTB_LDGF(&L.hi[2])), ray.o, ray.inv, t_max, &tl);
+    const bool hr = ex::slab(ex::v3(PTB_LDGF(&Rn.lo[0]), PTB_LDGF(&Rn.lo[1]), PTB_LDGF(&Rn.lo[2])), ex::v3(PTB_LDGF(&Rn.hi[0]), PTB_LDGF(&Rn.hi[1]), PTB_LDGF(&Rn.hi[2])), ray.o, ray.inv, t_max, &tr);
+    if (hl && hr)
+    {
+        if (tl < tr) { st[sp].id = r; st[sp++].t = tr; st[sp].id = l; st[sp++].t = tl; }
+        else { st[sp].id = l; st[sp++].t = tl; st[sp].id = r; st[sp++].t = tr; }
+    }
+    else if (hl) { st[sp].id = l; st[sp++].t = tl; }
+    else if (hr) { st[sp].id = r; st[sp++].t = tr; }
+}
+
+PTB_HD void load_planes(const SceneDev& S, uint32_t gtri, float n0[4], float n1[4], float n2[4])
+{
+    const float4* pp = S.planes_by_prim + (size_t)gtri * 3;
+    const float4 a = PTB_LDG4F(pp), b = PTB_LDG4F(pp + 1), c = PTB_LDG4F(pp + 2);
+    n0[0] = a.x; n0[1] = a.y; n0[2] = a.z; n0[3] = a.w;
+    n1[0] = b.x; n1[1] = b.y; n1[2] = b.z; n1[3] = b.w;
+    n2[0] = c.x; n2[1] = c.y; n2[2] = c.z; n2[3] = c.w;
+}
+
+template <bool ANY>
+PTB_HD bool bin_traverse(const SceneDev& S, int which, V3 o_world, V3 d_world, float t_max, Hit* hit)
+{
+    BinEntry st[BIN_STACK_CAP];
+    int sp = 0;
+    TravRay wray;
+    set_ray(wray, o_world, d_world);
+    const TlasDev& T = S.tlas[which];
+    const BinNode* nodes = S.bin;
+    bool found = false;
+    if (!ANY)
+    {
+        const BinNode& rt = nodes[T.bin_base + T.bin_root];  // tlas.rs:68
+        float te;
+        if (!ex::slab(ex::v3(rt.lo[0], rt.lo[1], rt.lo[2]), ex::v3(rt.hi[0], rt.hi[1], rt.hi[2]), wray.o, wray.inv, t_max, &te)) return false;
+    }
+    st[sp].id = T.bin_root;
+    st[sp++].t = 0.0f;
+    while (sp > 0)
+    {
+        const BinEntry cur = st[--sp];
+        const BinNode& n = nodes[T.bin_base + cur.id];
+        const uint32_t na = PTB_LDGU(&n.a), nb = PTB_LDGU(&n.b);
+        if (ANY)
+        {
+            float te;  // tlas.rs:118
+            if (!ex::slab(ex::v3(n.lo[0], n.lo[1], n.lo[2]), ex::v3(n.hi[0], n.hi[1], n.hi[2]), wray.o, wray.inv, t_max, &te)) continue;
+        }
+        else if (cur.t > t_max) continue;  // tlas.rs:80-83
+        if ((na >> BIN_KIND_SHIFT) == 0)
+        {
+            if (ANY) { st[sp].id = na; st[sp++].t = 0.0f; st[sp].id = nb; st[sp++].t = 0.0f; }  // tlas.rs:125-130
+            else bin_push2(nodes, T.bin_base, na, nb, wray, t_max, st, sp);
+            continue;
+        }
+        // TLAS leaf: transform and walk the BLAS with its own stack region above sp
+        const InstanceRow& R = S.inst[nb];
+        TravRay ray;
+        float inv12[12];
+        for (int k = 0; k < 12; ++k) inv12[k] = PTB_LDGF(R.inv + k);
+        transform_ray(ray, o_world, d_world, inv12);
+        const uint32_t bbase = PTB_LDGU(&R.bin_base), tri_base = PTB_LDGU(&R.tri_base), lp_base = PTB_LDGU(&R.leafprim_base);
+        const int floor_sp = sp;
+        st[sp].id = PTB_LDGU(&R.bin_root);
+        st[sp++].t = 0.0f;  // blas.rs:217: root pushed with 0.0, not box-tested (closest); any-hit tests every popped node (:264)
+        while (sp > floor_sp)
+        {
+            const BinEntry c = st[--sp];
+            const BinNode& bn = nodes[bbase + c.id];
+            const uint32_t a = PTB_LDGU(&bn.a), b = PTB_LDGU(&bn.b);
+            float t_enter = c.t;
+            if (ANY)
+            {
+                if (!ex::slab(ex::v3(bn.lo[0], bn.lo[1], bn.lo[2]), ex::v3(bn.hi[0], bn.hi[1], bn.hi[2]), ray.o, ray.inv, t_max, &t_enter)) continue;
+            }
+            else if (c.t > t_max) continue;
+            const uint32_t kind = a >> BIN_KIND_SHIFT, idx = a & BIN_INDEX_MASK;
+            if (kind == BIN_BRANCH)
+            {
+                if (ANY) { st[sp].id = idx; st[sp++].t = 0.0f; st[sp].id = b; st[sp++].t = 0.0f; }
+                else bin_push2(nodes, bbase, idx, b, ray, t_max, st, sp);
+                continue;
+            }
+            const uint32_t cnt = kind == BIN_LEAF_SINGLE ? 1u : b;
+            for (uint32_t k = 0; k < cnt; ++k)
+            {
+                const uint32_t prim = kind == BIN_LEAF_SINGLE ? idx : PTB_LDGU(S.leaf_prims + lp_base + idx + k);
+                float n0[4], n1[4], n2[4];
+                load_planes(S, tri_base + prim, n0, n1, n2);
+                if (ANY)
+                {
+                    if (ex::tri_hit_bool(n0, n1, n2, ray.o, ray.d, t_max, t_enter)) return true;
+                }
+                else
+                {
+                    float t, u, v;
+                    if (ex::tri_hit(n0, n1, n2, ray.o, ray.d, t_max, t_enter, &t, &u, &v))
+                    {
+                        t_max = t;
+                        hit->t = t; hit->u = u; hit->v = v; hit->slot_or_prim = prim; hit->inst = nb;
+                        found = true;
+                    }
+                }
+            }
+        }
+    }
+    return found;
+}
+
+}  // namespace ptb

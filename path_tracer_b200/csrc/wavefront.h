@@ -1,0 +1,378 @@
+// wavefront.h — the per-slot bodies of the wavefront stages (host+device), restating integrate() (integrator.rs:143-281)
+// and the frame loop (main.rs:181-207) as a state machine over SoA path state:
+//
+//   regen  : finish the previous sample of a slot (integrator.rs:272-280, accumulate.wgsl:23) and start the next one
+//            (main.rs:187-199: seed draw, Sobol jitter, Camera::create_ray)
+//   extend : scene.world.intersect (integrator.rs:179)
+//   shade  : everything between two intersect calls: b==0 bookkeeping, media, emission, volume set, NEE set-up,
+//            continuation, path weight, Russian roulette of the next bounce
+//   shadow : explicit light sample visibility + contribution (integrator.rs:56-70)
+//   probe  : BSDF-sampled direct light: lights-TLAS closest hit, world any-hit, contribution (integrator.rs:100-123)
+//
+// One slot == one pixel; a slot runs its pixel's samples back to back (path regeneration), so accum[pixel] has a single
+// writer and needs no atomics.  Queues between stages are handled by the callers (render.cu on the device, warp-aggregated;
+// tests/hostemu sequentially on the host): the bodies only return flags.
+#pragma once
+#include "../../include/ptb.h"
+#include "shading.h"
+#include "traverse.h"
+
+namespace ptb {
+
+struct RenderView
+{
+    SceneDev S;
+    CameraDev cam;
+    uint32_t W, H;
+    uint32_t sample_begin, sample_count;
+    unsigned long long seed;
+    uint32_t max_bounces;
+    uint32_t enable_nee;
+    uint32_t extend_kernel;  // 0 wide, 1 reference-order
+    // per pixel
+    float4* accum;     // (sum rgb, count)
+    float4* accum_sq;  // optional
+    float4* position;  // main.rs:205
+    uint32_t* id;      // main.rs:206
+    // per slot
+    float4* ray_o;     // o.xyz, w = bits: bounce (low 24) | last_delta << 24 | has_sample << 25
+    float4* ray_d;     // d.xyz, w = bits: samples started so far
+    float4* weight;    // path_weight.xyz
+    float4* radiance;  // accumulated.xyz
+    uint2* rng;
+    unsigned long long* volset;
+    float4* hit_tn;    // t, normal.xyz
+    uint32_t* hit_info;  // InstanceRow index | front << 31 ; 0xffffffff = miss
+    float4* nee_o;     // origin of this bounce's shadow and probe rays (the hit point)
+    float4* sh_d;      // shadow ray direction, w = t_max
+    float4* sh_c;      // contribution if unoccluded
+    float4* pr_d;      // probe direction, w = bsdf pdf
+    float4* pr_f;      // path_weight * weakening * bsdf / pdf
+};
+
+enum : uint32_t { WF_NEXT = 1u, WF_TERM = 2u, WF_SHADOW = 4u, WF_PROBE = 8u };
+constexpr uint32_t ST_LAST_DELTA = 1u << 24, ST_HAS_SAMPLE = 1u << 25, ST_BOUNCE_MASK = (1u << 24) - 1u;
+constexpr uint32_t Q_MISS = 6;  // shade queue kinds: 0..5 = material kinds, 6 = miss
+
+PTB_HD float4 f4(float x, float y, float z, float w)
+{
+    float4 r;
+    r.x = x; r.y = y; r.z = z; r.w = w;
+    return r;
+}
+
+// ---- regen ---------------------------------------------------------------------------------------------------------------
+PTB_HD uint32_t regen_slot(const RenderView& V, uint32_t slot)
+{
+    const uint32_t state = ex::bits(V.ray_o[slot].w);
+    uint32_t started = ex::bits(V.ray_d[slot].w);
+    if (state & ST_HAS_SAMPLE)
+    {
+        // integrator.rs:272-280 then accumulate.wgsl:23
+        const float4 r4 = V.radiance[slot];
+        V3 c = ex::v3(r4.x, r4.y, r4.z);
+        if (finite3(c))
+        {
+            const float l2 = dot(c, c);
+            if (l2 > 100.0f * 100.0f) c = c * ((1.0f / sqrtf(l2)) * 100.0f);  // clamp_length_max(100)
+        }
+        else c = ex::v3(0, 0, 0);
+        float4 a = V.accum[slot];
+        a.x += c.x; a.y += c.y; a.z += c.z; a.w += 1.0f;
+        V.accum[slot] = a;
+        if (V.accum_sq)
+        {
+            float4 q = V.accum_sq[slot];
+            q.x += c.x * c.x; q.y += c.y * c.y; q.z += c.z * c.z; q.w += 1.0f;
+            V.accum_sq[slot] = q;
+        }
+    }
+    if (started >= V.sample_count)
+    {
+        V.ray_o[slot].w = ex::from_bits(0u);
+        return 0u;
+    }
+    // main.rs:187-199
+    const uint32_t smp = V.sample_begin + started;
+    const uint32_t x = slot % V.W, y = slot / V.W;
+    Rng rng = rng_stream(V.seed, slot, smp);
+    const uint32_t jseed = rng_u32(rng);
+    float jx, jy;
+    ss_sobol(smp == 0u ? 0u : 1u, jseed, &jx, &jy);  // index = c.w as u32: 0 on the first frame, 1 afterwards (main.rs:194,204)
+    jx = ex::sub(jx, 0.5f);
+    jy = ex::sub(jy, 0.5f);
+    const float u = ex::div(ex::add((float)x, jx), (float)V.W), v = ex::div(ex::add((float)y, jy), (float)V.H);
+    V3 o, d;
+    camera_ray(V.cam, u, v, &o, &d);
+    V.ray_o[slot] = f4(o.x, o.y, o.z, ex::from_bits(ST_HAS_SAMPLE));  // bounce 0, last_delta false
+    V.ray_d[slot] = f4(d.x, d.y, d.z, ex::from_bits(started + 1u));
+    V.weight[slot] = f4(1.0f, 1.0f, 1.0f, 0.0f);
+    V.radiance[slot] = f4(0.0f, 0.0f, 0.0f, 0.0f);
+    uint2 rs;
+    rs.x = (uint32_t)rng.s;
+    rs.y = (uint32_t)(rng.s >> 32);
+    V.rng[slot] = rs;
+    if (V.volset) V.volset[slot] = 0ull;
+    // integrator.rs:156-157 defaults; overwritten at b == 0 on a hit
+    const V3 far = ex::ray_at(o, d, 1e5f);
+    V.position[slot] = f4(far.x, far.y, far.z, 1e5f);
+    V.id[slot] = (V.id[slot] << 16) | 255u;  // main.rs:206 with first_id defaulting to u8::MAX (integrator.rs:157)
+    return WF_NEXT;
+}
+
+// ---- extend --------------------------------------------------------------------------------------------------------------
+// returns the shade-queue kind (material kind of the hit BLAS, or Q_MISS)
+PTB_HD uint32_t extend_slot(const RenderView& V, uint32_t slot)
+{
+    const float4 o4 = V.ray_o[slot], d4 = V.ray_d[slot];
+    const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
+    Hit h;
+    h.inst = 0xffffffffu;
+    const bool f = V.extend_kernel ? bin_traverse<false>(V.S, 0, o, d, ex::inf(), &h) : wide_traverse<false>(V.S, 0, o, d, ex::inf(), &h);
+    if (!f)
+    {
+        V.hit_info[slot] = 0xffffffffu;
+        return Q_MISS;
+    }
+    const uint32_t prim = V.extend_kernel ? h.slot_or_prim : V.S.tri_prim[h.slot_or_prim];
+    V3 n;
+    bool ff;
+    finish_hit(V.S, d, h.inst, prim, h.u, h.v, &n, &ff);
+    V.hit_tn[slot] = f4(h.t, n.x, n.y, n.z);
+    V.hit_info[slot] = h.inst | (ff ? 0x80000000u : 0u);
+    return V.S.mat[V.S.inst[h.inst].blas].kind;
+}
+
+// ---- shade ---------------------------------------------------------------------------------------------------------------
+PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
+{
+    const float4 o4 = V.ray_o[slot], d4 = V.ray_d[slot];
+    const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
+    uint32_t state = ex::bits(o4.w);
+    const uint32_t b = state & ST_BOUNCE_MASK;
+    const bool last_delta = (state & ST_LAST_DELTA) != 0u;
+    const uint32_t info = V.hit_info[slot];
+    const float4 w4 = V.weight[slot];
+    V3 path_weight = ex::v3(w4.x, w4.y, w4.z);
+
+    if (info == 0xffffffffu)
+    {
+        // miss: integrator.rs:254-269
+        const float4 r4 = V.radiance[slot];
+        V3 acc = ex::v3(r4.x, r4.y, r4.z);
+        if (V.S.env)
+        {
+            const float u = fmaf(atan2f(d.x, d.z), INV_PI_F * 0.5f, 0.5f);
+            const float v = fmaf(asinf(d.y), -INV_PI_F, 0.5f);
+            acc = acc + env_bilinear(V.S.env, V.S.env_w, V.S.env_h, u, v) * path_weight;
+        }
+        else acc = acc + ex::v3(0.006f, 0.006f, 0.006f) * path_weight;
+        V.radiance[slot] = f4(acc.x, acc.y, acc.z, 0.0f);
+        return WF_TERM;
+    }
+
+    const float4 h4 = V.hit_tn[slot];
+    const float t = h4.x;
+    const V3 normal = ex::v3(h4.y, h4.z, h4.w);
+    const bool front = (info & 0x80000000u) != 0u;
+    const uint32_t inst = info & 0x7fffffffu;
+    const uint32_t blas = V.S.inst[inst].blas;
+    const Mat mat = load_mat(V.S.mat, blas);
+    const uint2 rs = V.rng[slot];
+    Rng rng;
+    rng.s = (unsigned long long)rs.x | ((unsigned long long)rs.y << 32);
+    const V3 hit_p = ex::ray_at(o, d, t);  // Ray::at (fused, ray.rs:20)
+
+    if (b == 0u)  // integrator.rs:181-185
+    {
+        V.position[slot] = f4(hit_p.x, hit_p.y, hit_p.z, t);
+        V.id[slot] = (V.id[slot] & 0xffff0000u) | (blas & 0xffu);  // first_id = id.index() as u8 (integrator.rs:184); history shifted in regen
+    }
+
+    uint32_t flags = 0u;
+    bool done = false, scattered = false;
+    V3 new_d = d, new_o = hit_p;
+    bool new_last_delta = last_delta;
+
+    // media: integrator.rs:189-205 (volume set iterated in table order)
+    unsigned long long vset = V.volset ? V.volset[slot] : 0ull;
+    if (vset)
+    {
+        float best_t = 0.0f;
+        V3 best_dir = ex::v3(0, 0, 0);
+        for (uint32_t vi = 0; vi < V.S.n_volumes; ++vi)
+        {
+            if (!((vset >> vi) & 1ull) || !(V.S.vol[vi].flags & 2u)) continue;
+            float ts;
+            V3 ds;
+            if (volume_scatter(V.S.vol[vi], rng, d, t, &ts, &ds))
+                if (!scattered || ex::total_lt(ts, best_t)) { best_t = ts; best_dir = ds; scattered = true; }
+        }
+        V3 trans = ex::v3(1, 1, 1);
+        for (uint32_t vi = 0; vi < V.S.n_volumes; ++vi)
+            if (((vset >> vi) & 1ull) && (V.S.vol[vi].flags & 1u)) trans = trans * volume_transmission(V.S.vol[vi], scattered ? best_t : t);
+        path_weight = path_weight * trans;
+        if (scattered)
+        {
+            new_last_delta = true;
+            new_o = ex::ray_at(o, d, best_t);
+            new_d = best_dir;
+        }
+    }
+
+    if (!scattered)
+    {
+        if (mat.kind == PTB_EMISSIVE)  // integrator.rs:207-214
+        {
+            if (!V.enable_nee || last_delta || b == 0u)
+            {
+                const float4 r4 = V.radiance[slot];
+                V.radiance[slot] = f4(fmaf(mat.colour.x, path_weight.x, r4.x), fmaf(mat.colour.y, path_weight.y, r4.y), fmaf(mat.colour.z, path_weight.z, r4.z), 0.0f);
+            }
+            done = true;
+        }
+        else
+        {
+            if (mat.volume >= 0 && V.volset)  // integrator.rs:217-227
+            {
+                if (front) vset |= (1ull << mat.volume);
+                else vset &= ~(1ull << mat.volume);
+                V.volset[slot] = vset;
+            }
+            const bool delta = is_delta(mat.kind);
+            const V3 wi = -d;
+            if (V.enable_nee && !delta)  // integrator.rs:231-234
+            {
+                // explicit light sample (integrator.rs:25-74): 1 + 2 draws, always
+                const uint32_t li = light_pick(V.S.lights, V.S.n_lights, rng_f32(rng));
+                const LightRow L = V.S.lights[li];
+                float lu = rng_f32(rng), lv = rng_f32(rng);
+                if (lu + lv > 1.0f) { lu = 1.0f - lu; lv = 1.0f - lv; }  // primitive.rs:77-91
+                const float* pp = V.S.tri_positions + (size_t)L.tri * 9;
+                const float* pn = V.S.tri_normals + (size_t)L.tri * 9;
+                const float lw = 1.0f - lu - lv;
+                const V3 point = (ex::v3(pp[0], pp[1], pp[2]) * lw + ex::v3(pp[3], pp[4], pp[5]) * lu) + ex::v3(pp[6], pp[7], pp[8]) * lv;
+                const V3 lnormal = normalizef((ex::v3(pn[0], pn[1], pn[2]) * lw + ex::v3(pn[3], pn[4], pn[5]) * lu) + ex::v3(pn[6], pn[7], pn[8]) * lv);
+                const V3 dl = point - hit_p;
+                const float dist2 = dot(dl, dl), dist = sqrtf(dist2);
+                const V3 ld = ex::normalize(dl);
+                if (dot(ld, normal) > 0.0f)
+                {
+                    const BsdfPdf bp = bsdf_pdf(mat, wi, ld, normal, front);
+                    const float4 n0 = V.S.planes_by_prim[(size_t)L.tri * 3];
+                    const float area = 0.5f * sqrtf((n0.x * n0.x + n0.y * n0.y) + n0.z * n0.z);  // Triangle::area
+                    const float sample_pdf = L.pdf / area;
+                    const float cosine = fabsf(dot(ld, lnormal));
+                    const float light_pdf = sample_pdf * (dist2 / cosine);
+                    const float wgt = (light_pdf * light_pdf) / (light_pdf * light_pdf + bp.pdf * bp.pdf);  // mis_heuristic<2>
+                    const Mat lmat = load_mat(V.S.mat, L.blas);
+                    const V3 c = path_weight * ((lmat.colour * wgt * weakening(mat.kind, ld, normal)) * bp.bsdf / light_pdf);
+                    V.nee_o[slot] = f4(hit_p.x, hit_p.y, hit_p.z, 0.0f);
+                    V.sh_d[slot] = f4(ld.x, ld.y, ld.z, (1.0f - ex::EPS) * dist);
+                    V.sh_c[slot] = f4(c.x, c.y, c.z, 0.0f);
+                    flags |= WF_SHADOW;
+                }
+                // BSDF-sampled light (integrator.rs:77-130): the material's draws, always
+                const V3 pd = scatter_direction(mat, rng, d, normal, front);
+                if (dot(pd, normal) > 0.0f)
+                {
+                    const BsdfPdf bp = bsdf_pdf(mat, wi, pd, normal, front);
+                    if (bp.pdf > 0.0f)  // MIN_PDF (checked upstream after the visibility tests; order is immaterial)
+                    {
+                        const V3 f = path_weight * (weakening(mat.kind, pd, normal) * bp.bsdf / bp.pdf);
+                        V.nee_o[slot] = f4(hit_p.x, hit_p.y, hit_p.z, 0.0f);
+                        V.pr_d[slot] = f4(pd.x, pd.y, pd.z, bp.pdf);
+                        V.pr_f[slot] = f4(f.x, f.y, f.z, 0.0f);
+                        flags |= WF_PROBE;
+                    }
+                }
+            }
+            // continuation: integrator.rs:236-251
+            new_d = scatter_direction(mat, rng, d, normal, front);
+            const BsdfPdf mi = bsdf_pdf(mat, wi, new_d, normal, front);
+            if (mi.pdf < 0.0f) done = true;
+            else
+            {
+                path_weight = path_weight * (weakening(mat.kind, new_d, normal) * mi.bsdf / mi.pdf);
+                new_last_delta = delta;
+            }
+        }
+    }
+
+    if (!done)
+    {
+        // next loop iteration: b+1 <= max_bounces, then Russian roulette (integrator.rs:163-177)
+        const uint32_t nb = b + 1u;
+        if (nb > V.max_bounces) done = true;
+        else if (nb > 3u)
+        {
+            const float survive = fminf(max3(path_weight), 0.9999f);
+            if (rng_f32(rng) > survive) done = true;
+            else path_weight = path_weight / survive;
+        }
+        if (!done)
+        {
+            state = (state & ~(ST_BOUNCE_MASK | ST_LAST_DELTA)) | nb | (new_last_delta ? ST_LAST_DELTA : 0u);
+            V.ray_o[slot] = f4(new_o.x, new_o.y, new_o.z, ex::from_bits(state));
+            V.ray_d[slot] = f4(new_d.x, new_d.y, new_d.z, d4.w);
+            V.weight[slot] = f4(path_weight.x, path_weight.y, path_weight.z, 0.0f);
+            uint2 ro;
+            ro.x = (uint32_t)rng.s;
+            ro.y = (uint32_t)(rng.s >> 32);
+            V.rng[slot] = ro;
+            return flags | WF_NEXT;
+        }
+    }
+    return flags | WF_TERM;
+}
+
+// ---- shadow --------------------------------------------------------------------------------------------------------------
+PTB_HD void shadow_slot(const RenderView& V, uint32_t slot)
+{
+    const float4 o4 = V.nee_o[slot], d4 = V.sh_d[slot];
+    Hit h;
+    const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
+    const bool occluded = V.extend_kernel ? bin_traverse<true>(V.S, 0, o, d, d4.w, &h) : wide_traverse<true>(V.S, 0, o, d, d4.w, &h);
+    if (occluded) return;
+    const float4 c = V.sh_c[slot];
+    float4 r = V.radiance[slot];
+    r.x += c.x; r.y += c.y; r.z += c.z;
+    V.radiance[slot] = r;
+}
+
+// ---- probe ---------------------------------------------------------------------------------------------------------------
+// returns 1 when the lights-TLAS probe hit a light and a world shadow ray was traced
+PTB_HD uint32_t probe_slot(const RenderView& V, uint32_t slot)
+{
+    const float4 o4 = V.nee_o[slot], d4 = V.pr_d[slot];
+    const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
+    Hit h;
+    h.inst = 0xffffffffu;
+    const bool lit = V.extend_kernel ? bin_traverse<false>(V.S, 1, o, d, ex::inf(), &h) : wide_traverse<false>(V.S, 1, o, d, ex::inf(), &h);  // integrator.rs:100
+    if (!lit) return 0u;
+    Hit dummy;
+    const float tl = h.t;
+    const bool occluded = V.extend_kernel ? bin_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy) : wide_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy);  // :103
+    if (occluded) return 1u;
+    const uint32_t prim = V.extend_kernel ? h.slot_or_prim : V.S.tri_prim[h.slot_or_prim];
+    V3 ln;
+    bool ff;
+    finish_hit(V.S, d, h.inst, prim, h.u, h.v, &ln, &ff);
+    const InstanceRow& R = V.S.inst[h.inst];
+    const Mat lmat = load_mat(V.S.mat, R.blas);
+    // get_sample_pdf(light, material) / light.area()  (light_sampler.rs:39, integrator.rs:111)
+    const float4 n0 = V.S.planes_by_prim[(size_t)(R.tri_base + prim) * 3];
+    const float area = 0.5f * sqrtf((n0.x * n0.x + n0.y * n0.y) + n0.z * n0.z);
+    const float sample_pdf = (area * sqrtf(dot(lmat.colour, lmat.colour)) / V.S.light_max) / area;
+    const float cosine = fabsf(dot(d, ln));
+    const float light_pdf = sample_pdf * (tl * tl / cosine);
+    const float bp = d4.w;
+    const float wgt = (bp * bp) / (bp * bp + light_pdf * light_pdf);  // mis_heuristic<2>(bsdf_pdf, light_pdf)
+    const float4 f = V.pr_f[slot];
+    float4 r = V.radiance[slot];
+    r.x += lmat.colour.x * wgt * f.x; r.y += lmat.colour.y * wgt * f.y; r.z += lmat.colour.z * wgt * f.z;
+    V.radiance[slot] = r;
+    return 1u;
+}
+
+}  // namespace ptb

@@ -1,0 +1,101 @@
+"""ctypes wrapper of tests/hostemu/libhostemu.so — TEST-ONLY host build of the product's traversal code."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        subprocess.check_call(["make", "-C", _HERE, "-s"], stderr=subprocess.DEVNULL)
+        _LIB = C.CDLL(os.path.join(_HERE, "libhostemu.so"))
+        _LIB.emu_create.restype = C.c_void_p
+    return _LIB
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class EmuScene:
+    def __init__(self, sd, pack_scene, threads=0):
+        verts, bd, inst = pack_scene(sd)
+        self._keep = (verts, bd, inst)
+        err = C.create_string_buffer(512)
+        self.h = lib().emu_create(_p(verts), C.c_uint64(verts.shape[0]), C.byref(bd), len(sd.blas), C.byref(inst), len(sd.instances), threads, err, 512)
+        if not self.h:
+            raise ValueError(err.value.decode())
+
+    def close(self):
+        if self.h:
+            lib().emu_destroy(C.c_void_p(self.h))
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def stats(self):
+        out = np.zeros(8, np.uint64)
+        lib().emu_stats(C.c_void_p(self.h), _p(out))
+        return out
+
+    def trace(self, o, d, tmax, which=0, kernel=0, any_hit=False, threads=0):
+        n = o.shape[0]
+        o, d, tmax = (np.ascontiguousarray(x, np.float32) for x in (o, d, tmax))
+        out = dict(hit=np.zeros(n, np.uint8), t=np.zeros(n, np.float32), u=np.zeros(n, np.float32), v=np.zeros(n, np.float32), prim=np.zeros(n, np.uint32),
+                   blas=np.zeros(n, np.uint32), inst=np.zeros(n, np.uint32), front=np.zeros(n, np.uint8), normal=np.zeros((n, 3), np.float32))
+        lib().emu_trace(C.c_void_p(self.h), which, kernel, int(any_hit), C.c_uint64(n), _p(o), _p(d), _p(tmax), _p(out["hit"]), _p(out["t"]), _p(out["u"]), _p(out["v"]),
+                        _p(out["prim"]), _p(out["blas"]), _p(out["inst"]), _p(out["front"]), _p(out["normal"]), threads)
+        return out
+
+
+def camera(origin, target, fov_deg, aspect):
+    m = np.zeros(16, np.float32)
+    eye = np.zeros(3, np.float32)
+    o = np.asarray(origin, np.float32)
+    t = np.asarray(target, np.float32)
+    lib().emu_camera(_p(o), _p(t), C.c_float(fov_deg), C.c_float(aspect), _p(m), _p(eye))
+    return m, eye
+
+
+def camera_rays(origin, target, fov_deg, aspect, st):
+    m, eye = camera(origin, target, fov_deg, aspect)
+    st = np.ascontiguousarray(st, np.float32)
+    n = st.shape[0]
+    o = np.zeros((n, 3), np.float32)
+    d = np.zeros((n, 3), np.float32)
+    lib().emu_camera_rays(_p(m), _p(eye), C.c_uint64(n), _p(st), _p(o), _p(d))
+    return o, d
+
+
+def ss_sobol(index, seed):
+    index = np.ascontiguousarray(index, np.uint32)
+    seed = np.ascontiguousarray(seed, np.uint32)
+    out = np.zeros((index.shape[0], 2), np.float32)
+    lib().emu_ss_sobol(C.c_uint64(index.shape[0]), _p(index), _p(seed), _p(out))
+    return out
+
+
+def rng_stream(seed, pixel, sample, n):
+    out = np.zeros(n, np.uint32)
+    lib().emu_rng_stream(C.c_uint64(seed), pixel, sample, n, _p(out))
+    return out
+
+
+def render(es, sd, width, height, sample_begin=0, sample_count=1, seed=1, max_bounces=None, enable_nee=True, extend_kernel=0):
+    m, eye = camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(width) / np.float32(height))
+    accum = np.zeros((height, width, 4), np.float32)
+    pos = np.zeros((height, width, 4), np.float32)
+    ids = np.zeros((height, width), np.uint32)
+    cnt = np.zeros(5, np.uint64)
+    mb = sd.max_bounces if max_bounces is None else max_bounces
+    lib().emu_render(C.c_void_p(es.h), _p(m), _p(eye), width, height, sample_begin, sample_count, C.c_uint64(seed), mb, int(enable_nee), extend_kernel, _p(accum), _p(pos), _p(ids), _p(cnt))
+    return dict(accum=accum, position=pos, id=ids, counters=dict(extend=int(cnt[0]), shadow=int(cnt[1]), probe=int(cnt[2]), paths=int(cnt[3]), iters=int(cnt[4])))

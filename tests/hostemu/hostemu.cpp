@@ -1,0 +1,187 @@
+// tests/hostemu — TEST-ONLY harness: compiles the product's __host__ __device__ traversal code (csrc/traverse.h)
+// for the CPU so its logic can be checked against the oracle in the GPU-less container.  It is never linked into
+// libptb.so and no C-ABI entry point routes here: the product has no CPU path (ptb_* compute calls return
+// PTB_ERR_NO_DEVICE without a GPU).
+#include <atomic>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../path_tracer_b200/csrc/camera_host.h"
+#include "../../path_tracer_b200/csrc/host_scene.h"
+#include "../../path_tracer_b200/csrc/traverse.h"
+#include "../../path_tracer_b200/csrc/wavefront.h"
+
+using namespace ptb;
+
+extern "C" {
+
+void* emu_create(const float* verts, uint64_t ntri, const ptb_blas_desc* blas, uint32_t nblas, const ptb_instance* inst, uint32_t ninst, int threads, char* err, int errlen)
+{
+    auto* sc = new HostScene();
+    std::string e;
+    int rc = sc->upload(verts, ntri, blas, nblas, inst, ninst, e);
+    if (rc == PTB_OK) rc = sc->build(threads, e);
+    if (rc != PTB_OK)
+    {
+        if (err && errlen > 0) { std::strncpy(err, e.c_str(), errlen - 1); err[errlen - 1] = 0; }
+        delete sc;
+        return nullptr;
+    }
+    return sc;
+}
+void emu_destroy(void* h) { delete (HostScene*)h; }
+
+void emu_trace(void* h, int which, int kernel, int any, uint64_t n, const float* o, const float* d, const float* tmax, uint8_t* hit, float* t, float* u, float* v,
+               uint32_t* prim, uint32_t* blas, uint32_t* inst, uint8_t* front, float* normal, int threads)
+{
+    const HostScene& sc = *(HostScene*)h;
+    const SceneDev S = host_view(sc);
+    if (threads <= 0) threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    std::atomic<uint64_t> next{0};
+    auto work = [&] {
+        for (;;)
+        {
+            uint64_t b = next.fetch_add(1024);
+            if (b >= n) break;
+            uint64_t e = std::min(n, b + 1024);
+            for (uint64_t i = b; i < e; ++i)
+            {
+                V3 ro = ex::v3(o[i * 3], o[i * 3 + 1], o[i * 3 + 2]), rd = ex::v3(d[i * 3], d[i * 3 + 1], d[i * 3 + 2]);
+                Hit hr{};
+                bool f;
+                if (any) f = kernel ? bin_traverse<true>(S, which, ro, rd, tmax[i], &hr) : wide_traverse<true>(S, which, ro, rd, tmax[i], &hr);
+                else f = kernel ? bin_traverse<false>(S, which, ro, rd, tmax[i], &hr) : wide_traverse<false>(S, which, ro, rd, tmax[i], &hr);
+                hit[i] = f;
+                if (any) continue;
+                uint32_t p = 0xffffffffu, ib = 0xffffffffu, ii = 0xffffffffu;
+                V3 nn = ex::v3(0, 0, 0);
+                bool ff = false;
+                if (f)
+                {
+                    p = kernel ? hr.slot_or_prim : S.tri_prim[hr.slot_or_prim];
+                    ib = S.inst[hr.inst].blas;
+                    ii = hr.inst - S.tlas[which].inst_base;
+                    finish_hit(S, rd, hr.inst, p, hr.u, hr.v, &nn, &ff);
+                }
+                if (t) t[i] = f ? hr.t : ex::inf();
+                if (u) u[i] = f ? hr.u : 0.0f;
+                if (v) v[i] = f ? hr.v : 0.0f;
+                if (prim) prim[i] = p;
+                if (blas) blas[i] = ib;
+                if (inst) inst[i] = ii;
+                if (front) front[i] = ff;
+                if (normal) { normal[i * 3] = nn.x; normal[i * 3 + 1] = nn.y; normal[i * 3 + 2] = nn.z; }
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (int k = 0; k < threads; ++k) th.emplace_back(work);
+    for (auto& x : th) x.join();
+}
+
+// canonical dump, same shapes as ptb_bvh_* (lets the CPU tests check the builder before the C ABI exists on a box)
+void emu_blas_counts(void* h, uint32_t b, uint32_t* nc, uint32_t* lc, uint32_t* root)
+{
+    const HostBlas& B = ((HostScene*)h)->blas[b];
+    *nc = (uint32_t)B.nodes.size();
+    *lc = (uint32_t)B.leaf_prims.size();
+    *root = B.root;
+}
+void emu_stats(void* h, uint64_t* out8)
+{
+    const HostScene& sc = *(HostScene*)h;
+    out8[0] = sc.wide.size();
+    out8[1] = sc.leaf_headers.size();
+    out8[2] = sc.tri_prim.size();
+    out8[3] = sc.wide.size() * 80 + sc.leaf_headers.size() * 32 + sc.tri_prim.size() * 52;
+    out8[4] = 0;
+    for (auto& B : sc.blas) out8[4] = std::max<uint64_t>(out8[4], B.wide_depth);
+    out8[4] += sc.tlas[0].wide_depth;
+    out8[5] = sc.bin.size();
+    out8[6] = sc.inst_rows.size();
+    out8[7] = sc.wide_stack_bound;
+}
+
+// Sequential emulation of the wavefront loop of render.cu using the very same per-slot bodies (wavefront.h).
+// cam16: ray matrix (column-major) as ptb_set_camera computes it is NOT available here (render.cu is device code), so the
+// caller passes the camera matrix + eye obtained from the oracle-independent helper emu_camera below.
+void emu_render(void* h, const float* cam_m16, const float* cam_eye3, uint32_t W, uint32_t H, uint32_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_bounces,
+                int enable_nee, int extend_kernel, float* accum, float* position, uint32_t* id, uint64_t* counters)
+{
+    const HostScene& sc = *(HostScene*)h;
+    const uint32_t npix = W * H;
+    RenderView V{};
+    V.S = host_view(sc);
+    std::memcpy(V.cam.m, cam_m16, 64);
+    std::memcpy(V.cam.eye, cam_eye3, 12);
+    V.W = W; V.H = H; V.sample_begin = sample_begin; V.sample_count = sample_count; V.seed = seed; V.max_bounces = max_bounces;
+    V.enable_nee = enable_nee ? 1u : 0u;
+    V.extend_kernel = extend_kernel ? 1u : 0u;
+    std::vector<float4> ray_o(npix), ray_d(npix), weight(npix), radiance(npix), hit_tn(npix), nee_o(npix), sh_d(npix), sh_c(npix), pr_d(npix), pr_f(npix);
+    std::vector<uint2> rng(npix);
+    std::vector<unsigned long long> volset(npix);
+    std::vector<uint32_t> hit_info(npix);
+    V.accum = (float4*)accum; V.accum_sq = nullptr; V.position = (float4*)position; V.id = id;
+    V.ray_o = ray_o.data(); V.ray_d = ray_d.data(); V.weight = weight.data(); V.radiance = radiance.data(); V.rng = rng.data();
+    V.volset = sc.volumes.empty() ? nullptr : volset.data();
+    V.hit_tn = hit_tn.data(); V.hit_info = hit_info.data(); V.nee_o = nee_o.data(); V.sh_d = sh_d.data(); V.sh_c = sh_c.data(); V.pr_d = pr_d.data(); V.pr_f = pr_f.data();
+    std::vector<uint32_t> ext, next, term, shadow, probe;
+    for (uint32_t i = 0; i < npix; ++i) { ray_o[i].w = 0.0f; ray_d[i].w = 0.0f; term.push_back(i); }
+    uint64_t n_extend = 0, n_shadow = 0, n_probe = 0, n_paths = 0, n_iters = 0;
+    for (;;)
+    {
+        for (uint32_t s : term) if (regen_slot(V, s) & WF_NEXT) { next.push_back(s); ++n_paths; }
+        term.clear();
+        ext.swap(next);
+        next.clear();
+        if (ext.empty()) break;
+        ++n_iters;
+        // material-sorted shade order, as the device queues: kinds 0..6
+        std::vector<uint32_t> mat[7];
+        for (uint32_t s : ext) mat[extend_slot(V, s)].push_back(s);
+        n_extend += ext.size();
+        for (int k = 0; k < 7; ++k)
+            for (uint32_t s : mat[k])
+            {
+                const uint32_t f = shade_slot(V, s);
+                if (f & WF_SHADOW) shadow.push_back(s);
+                if (f & WF_PROBE) probe.push_back(s);
+                if (f & WF_NEXT) next.push_back(s);
+                if (f & WF_TERM) term.push_back(s);
+            }
+        for (uint32_t s : shadow) shadow_slot(V, s);
+        n_shadow += shadow.size();
+        for (uint32_t s : probe) n_shadow += probe_slot(V, s);
+        n_probe += probe.size();
+        shadow.clear();
+        probe.clear();
+    }
+    if (counters) { counters[0] += n_extend; counters[1] += n_shadow; counters[2] += n_probe; counters[3] += n_paths; counters[4] += n_iters; }
+}
+
+void emu_ss_sobol(uint64_t n, const uint32_t* index, const uint32_t* seed, float* xy)
+{
+    for (uint64_t i = 0; i < n; ++i) ss_sobol(index[i], seed[i], &xy[i * 2], &xy[i * 2 + 1]);
+}
+void emu_rng_stream(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t n, uint32_t* out)
+{
+    Rng r = rng_stream(seed, pixel, sample);
+    for (uint32_t i = 0; i < n; ++i) out[i] = rng_u32(r);
+}
+void emu_camera_rays(const float* cam_m16, const float* cam_eye3, uint64_t n, const float* st, float* o3, float* d3)
+{
+    CameraDev c;
+    std::memcpy(c.m, cam_m16, 64);
+    std::memcpy(c.eye, cam_eye3, 12);
+    for (uint64_t i = 0; i < n; ++i)
+    {
+        V3 o, d;
+        camera_ray(c, st[i * 2], st[i * 2 + 1], &o, &d);
+        o3[i * 3] = o.x; o3[i * 3 + 1] = o.y; o3[i * 3 + 2] = o.z;
+        d3[i * 3] = d.x; d3[i * 3 + 1] = d.y; d3[i * 3 + 2] = d.z;
+    }
+}
+void emu_camera(const float* origin, const float* target, float fov_deg, float aspect, float* m16, float* eye3) { camera_setup(origin, target, fov_deg, aspect, m16, eye3); }
+}
