@@ -1,0 +1,145 @@
+"""Bit-exact build output: product builder (through the C ABI, host-only context) vs the oracle's
+literal restatement of blas_bvh.rs / tlas_bvh.rs / light_sampler.rs."""
+import numpy as np
+import pytest
+
+from conftest import bits
+
+
+def _assert_same_blas(a, b):
+    assert a["root"] == b["root"]
+    assert np.array_equal(a["meta"], b["meta"])
+    assert np.array_equal(bits(a["boxes"]), bits(b["boxes"]))
+    assert np.array_equal(a["leaf_prims"], b["leaf_prims"])
+    assert np.array_equal(bits(a["triangles"]), bits(b["triangles"]))
+
+
+def _check_scene(po, sd, threads=0):
+    import path_tracer_b200 as ptb
+    ctx = ptb.Context(-1)
+    ctx.upload(sd, threads=threads)
+    sc = po.OracleScene(sd)
+    for b in range(len(sd.blas)):
+        _assert_same_blas(sc.blas_dump(b), ctx.blas_dump(b))
+    for which in (0, 1):
+        x, y = sc.tlas_dump(which), ctx.tlas_dump(which)
+        assert x["root"] == y["root"]
+        assert np.array_equal(x["meta"], y["meta"])
+        assert np.array_equal(bits(x["boxes"]), bits(y["boxes"]))
+        assert np.array_equal(bits(x["matrices"]), bits(y["matrices"]))
+        assert np.array_equal(x["blas_ids"], y["blas_ids"])
+    x, y = sc.light_sampler(), ctx.light_sampler()
+    assert np.array_equal(x["items"], y["items"])
+    for k in ("pdf", "cdf"):
+        assert np.array_equal(bits(x[k]), bits(y[k]))
+    assert bits(np.float32(x["max"])) == bits(np.float32(y["max"]))
+    return ctx
+
+
+@pytest.mark.parametrize("name", ["c1", "c2", "c3_small", "materials", "furnace", "c4_small"])
+def test_build_bit_exact(po, scenes, name):
+    sd = {"c1": scenes.scene_c1, "c2": scenes.scene_c2, "c3_small": lambda: scenes.scene_c3(grid=6), "materials": scenes.scene_materials_test,
+          "furnace": scenes.scene_furnace, "c4_small": lambda: scenes.scene_c4(nverts=120, n_spheres=6)}[name]()
+    _check_scene(po, sd)
+    _check_scene(po, sd, threads=1)  # sub-tree parallelism must not change ids
+
+
+def _soup_scene(scenes, tris, extra=None):
+    b = scenes._Builder()
+    light = scenes.quad((-1, 50, -1), (1, 50, -1), (1, 50, 1), (-1, 50, 1))
+    b.add_blas(scenes._tri_soup(light), scenes.material(scenes.EMISSIVE, (1, 1, 1)))
+    b.add_blas(scenes._tri_soup(tris), scenes.material(scenes.LAMBERTIAN, (0.5, 0.5, 0.5)), matrices=extra or (scenes.IDENTITY,))
+    return scenes.SceneData("soup", b.verts(), b.blas, b.instances, (0, 0, 100), (0, 0, 0), 60.0, 32, 32, 1, 8)
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 7, 64, 127, 128, 129, 1000, 5000])
+def test_random_soups_all_split_candidate_regimes(po, scenes, n):
+    # n < 128: n-1 candidates; n >= 128: 63..126 candidates of bin size n/64 (blas_bvh.rs:93-99)
+    rng = np.random.default_rng(n)
+    c = rng.uniform(-100, 100, size=(n, 1, 3))
+    tris = (c + rng.normal(0, 3.0, size=(n, 3, 3))).astype(np.float32)
+    _check_scene(po, _soup_scene(scenes, tris))
+
+
+def test_degenerate_inputs(po, scenes):
+    rng = np.random.default_rng(5)
+    # duplicated triangles (equal sort keys -> stability matters), flat boxes (SA = 0 -> inf / NaN costs), signed zeros
+    base = (rng.uniform(-10, 10, size=(40, 1, 3)) + rng.normal(0, 1, size=(40, 3, 3))).astype(np.float32)
+    dup = np.concatenate([base, base, base[:13]])
+    _check_scene(po, _soup_scene(scenes, dup))
+    flat = dup.copy()
+    flat[:, :, 1] = 0.0  # everything in the plane y = 0
+    _check_scene(po, _soup_scene(scenes, flat))
+    line = dup.copy()
+    line[:, :, 1] = 0.0
+    line[:, :, 2] = 0.0  # zero surface area boxes everywhere: 0/0 = NaN costs -> "split" branch of blas_bvh.rs:114
+    _check_scene(po, _soup_scene(scenes, line))
+    grid = np.zeros((300, 3, 3), np.float32)  # many equal minima on every axis
+    ij = np.arange(300)
+    grid[:, :, 0] = (ij % 5)[:, None] + np.array([0, 1, 0])[None, :]
+    grid[:, :, 2] = (ij // 5 % 5)[:, None] + np.array([0, 0, 1])[None, :]
+    _check_scene(po, _soup_scene(scenes, grid))
+    # many instances with 90-degree rotations: agglomerative TLAS (tlas_bvh.rs:106-135) incl. ties between equal boxes
+    mats = [scenes.rot_y90(k % 4, ((k % 7) * 30.0, 0.0, (k // 7) * 30.0)) for k in range(60)]
+    _check_scene(po, _soup_scene(scenes, base, extra=mats))
+    mats = [scenes.translate(((k % 5) * 25.0, 0.0, 0.0)) for k in range(10)] * 2  # exactly coincident instances
+    _check_scene(po, _soup_scene(scenes, base, extra=mats))
+
+
+def test_large_build_properties_and_subtrees(po, scenes):
+    """At a size the literal O(k n) restatement cannot build quickly, check size-independent properties and re-derive
+    random sub-trees of the product's output with the restatement (po.generate_blas_span)."""
+    import path_tracer_b200 as ptb
+    sd = scenes.scene_c4(nverts=420, n_spheres=4)  # ~351k terrain triangles
+    ctx = ptb.Context(-1)
+    ctx.upload(sd)
+    d = ctx.blas_dump(1)
+    meta, boxes, lp = d["meta"], d["boxes"], d["leaf_prims"]
+    n = meta.shape[0]
+    ntri = sd.blas[1][1]
+    assert d["root"] == n - 1
+    br = meta[:, 0] == 0
+    assert np.all(meta[br, 1] < np.nonzero(br)[0]) and np.all(meta[br, 2] < np.nonzero(br)[0])
+    assert np.array_equal(bits(boxes[br, :3]), bits(np.minimum(boxes[meta[br, 1], :3], boxes[meta[br, 2], :3])))
+    assert np.array_equal(bits(boxes[br, 3:]), bits(np.maximum(boxes[meta[br, 1], 3:], boxes[meta[br, 2], 3:])))
+    seen = np.zeros(ntri, np.int64)
+    np.add.at(seen, meta[meta[:, 0] == 1, 1], 1)
+    for a, c in meta[meta[:, 0] == 2][:, 1:]:
+        np.add.at(seen, lp[a:a + c], 1)
+    assert np.all(seen == 1)
+    # sub-tree sizes and ordered leaf spans via post-order structure
+    size = np.ones(n, np.int64)
+    for i in np.nonzero(br)[0]:
+        size[i] = 1 + size[meta[i, 1]] + size[meta[i, 2]]
+    tri = d["triangles"]
+    pbox = np.concatenate([np.minimum(np.minimum(tri[:, 0:3], tri[:, 3:6]), tri[:, 6:9]), np.maximum(np.maximum(tri[:, 0:3], tri[:, 3:6]), tri[:, 6:9])], axis=1)
+    rng = np.random.default_rng(3)
+    cands = [i for i in np.nonzero(br)[0] if 200 < size[i] < 20000]
+    checked = 0
+    for i in rng.choice(cands, size=6, replace=False):
+        lo = i - size[i] + 1  # post-order: the sub-tree occupies ids [lo, i]
+        sub = meta[lo:i + 1]
+        prims = []
+        for k, a, c in sub:  # leaves appear in span order
+            if k == 1:
+                prims.append(a)
+            elif k == 2:
+                prims.extend(lp[a:a + c])
+        prims = np.array(prims, np.uint32)
+        # the span order is the order after this node's own sort; re-running with the node's own axis as "last axis" must reproduce it
+        ext = boxes[i, 3:] - boxes[i, :3]
+        axis = 0 if ext[0] == ext.max() else (1 if ext[1] == ext.max() else 2)
+        r = po.generate_blas_span(pbox[prims], prims, last_axis=axis)
+        assert r["meta"].shape[0] == size[i]
+        assert np.array_equal(bits(r["boxes"]), bits(boxes[lo:i + 1]))
+        rk, sk = r["meta"].copy(), sub.copy()
+        rb = rk[:, 0] == 0
+        sk[rb, 1:] -= np.uint32(lo)  # child ids relative to the sub-tree
+        assert np.array_equal(rk[:, 0], sk[:, 0]) and np.array_equal(rk[rb], sk[rb])
+        assert np.array_equal(rk[rk[:, 0] == 1, 1], sk[sk[:, 0] == 1, 1])
+        l2 = rk[:, 0] == 2
+        assert np.array_equal(rk[l2, 2], sk[l2, 2])
+        for (_, a1, c1), (_, a2, c2) in zip(rk[l2], sk[l2]):
+            assert np.array_equal(r["leaf_prims"][a1:a1 + c1], lp[a2:a2 + c2])
+        checked += 1
+    assert checked == 6

@@ -1,0 +1,82 @@
+"""CPU unit tests of the product's __host__ __device__ code (tests/hostemu): traversal and wavefront bodies compiled for
+the host and compared with the oracle.  This is a logic check that runs in the GPU-less container; the parity tests
+proper are the `gpu` ones that call the CUDA kernels through the C ABI."""
+import numpy as np
+import pytest
+
+from conftest import bits, compare_closest
+
+
+@pytest.fixture(scope="module")
+def emu():
+    import emu as _emu
+    _emu.lib()
+    return _emu
+
+
+def _batches(po, scenes, sd, n):
+    st = scenes.pixel_centre_st(sd.width, sd.height, stride=max(1, int((sd.width * sd.height / n) ** 0.5)))
+    o, d = po.camera_rays(sd.cam_origin, sd.cam_target, sd.fov_deg, sd.aspect, st)
+    yield "primary", o, d, np.full(o.shape[0], np.inf, np.float32)
+    yield ("incoherent",) + scenes.incoherent_rays(sd, n)
+    yield ("incoherent_finite",) + scenes.incoherent_rays(sd, n, seed=99, finite_tmax=True)
+
+
+@pytest.mark.parametrize("name", ["c2", "c1", "c3_small", "materials", "c4_small"])
+def test_traversal_matches_oracle(po, scenes, emu, name):
+    sd = {"c1": scenes.scene_c1, "c2": scenes.scene_c2, "c3_small": lambda: scenes.scene_c3(grid=8), "materials": scenes.scene_materials_test,
+          "c4_small": lambda: scenes.scene_c4(nverts=150, n_spheres=8)}[name]()
+    sc = po.OracleScene(sd)
+    es = emu.EmuScene(sd, po.pack_scene)
+    ties = 0
+    for _, o, d, tm in _batches(po, scenes, sd, 30000):
+        for which in (0, 1):
+            ref = sc.trace_closest(o, d, tm, which=which)
+            ref_any = sc.trace_any(o, d, tm, which=which)
+            # reference-order kernel: bit-exact, no ties allowed
+            got = es.trace(o, d, tm, which=which, kernel=1)
+            compare_closest(ref, got, sc, o, d, tm, which=which, allow_ties=False)
+            assert np.array_equal(es.trace(o, d, tm, which=which, kernel=1, any_hit=True)["hit"], ref_any["hit"])
+            # 8-wide kernel: bit-exact up to classified ties
+            got = es.trace(o, d, tm, which=which, kernel=0)
+            ties += compare_closest(ref, got, sc, o, d, tm, which=which)[1]
+            assert np.array_equal(es.trace(o, d, tm, which=which, kernel=0, any_hit=True)["hit"], ref_any["hit"])
+    assert ties < 200
+
+
+def test_integer_tier_bit_exact(po, emu):
+    idx = (np.arange(20000, dtype=np.uint32) * 7) % 5
+    seeds = (np.arange(20000, dtype=np.uint32) * np.uint32(2654435761)).astype(np.uint32)
+    assert np.array_equal(bits(po.ss_sobol(idx, seeds)), bits(emu.ss_sobol(idx, seeds)))
+    for s, p, k in ((1, 0, 0), (77, 12345, 9), (2**63 + 5, 2**31 + 1, 4095)):
+        assert np.array_equal(po.rng_stream(s, p, k, 256), emu.rng_stream(s, p, k, 256))
+
+
+def test_camera_rays(po, scenes, emu):
+    sd = scenes.scene_c2()
+    st = scenes.pixel_centre_st(320, 180)
+    o1, d1 = po.camera_rays(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(320 / 180), st)
+    o2, d2 = emu.camera_rays(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(320 / 180), st)
+    assert np.array_equal(o1, o2) and np.abs(d1 - d2).max() <= 2e-7  # tolerance tier; observed bit-equal
+
+
+@pytest.mark.parametrize("name,nee", [("c2", True), ("c2", False), ("c1", True), ("materials", True)])
+def test_wavefront_matches_integrate_path_by_path(po, scenes, emu, name, nee):
+    """Same RNG streams -> the wavefront state machine must trace the same paths as the recursive-loop restatement."""
+    sd = {"c1": scenes.scene_c1, "c2": scenes.scene_c2, "materials": scenes.scene_materials_test}[name]()
+    sc = po.OracleScene(sd)
+    es = emu.EmuScene(sd, po.pack_scene)
+    W, H, N = 64, 36, 6
+    a = sc.render(width=W, height=H, sample_count=N, seed=5, enable_nee=nee)
+    b = emu.render(es, sd, W, H, sample_count=N, seed=5, enable_nee=nee)
+    for k in ("extend", "shadow", "probe", "paths"):
+        assert abs(a["counters"][k] - b["counters"][k]) <= 0.002 * a["counters"][k] + 2
+    assert np.array_equal(a["id"], b["id"])
+    A, B = a["accum"][..., :3] / N, b["accum"][..., :3] / N
+    rel = np.abs(A - B).max(axis=2) / (np.abs(A).max(axis=2) + 1e-3)
+    assert (rel > 1e-3).mean() < 0.01
+    assert np.all(b["accum"][..., 3] == N)
+    # splitting the sample range reproduces the same sums (streams are keyed by global sample index)
+    c1 = emu.render(es, sd, W, H, sample_begin=0, sample_count=2, seed=5, enable_nee=nee)
+    c2 = emu.render(es, sd, W, H, sample_begin=2, sample_count=4, seed=5, enable_nee=nee)
+    assert np.allclose(c1["accum"] + c2["accum"], b["accum"], rtol=1e-5, atol=1e-6)
