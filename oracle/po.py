@@ -184,13 +184,13 @@ class OracleScene:
         sq = np.zeros((H, W, 4), np.float32) if want_sq else None
         pos = np.zeros((H, W, 4), np.float32)
         ids = np.zeros((H, W), np.uint32)
-        cnt = np.zeros(11, np.uint64)
+        cnt = np.zeros(14, np.uint64)
         org = np.asarray(cam[0] if cam else sd.cam_origin, np.float32)
         tgt = np.asarray(cam[1] if cam else sd.cam_target, np.float32)
         aspect = np.float32(W) / np.float32(H)
         secs = lib().po_render(C.c_void_p(self.h), _p(org), _p(tgt), C.c_float(sd.fov_deg), C.c_float(aspect), W, H, sample_begin, sample_count, C.c_uint64(seed), mb,
                                int(enable_nee), threads, _p(accum), _p(sq), _p(pos), _p(ids), _p(cnt))
-        names = ["extend", "shadow", "probe", "paths", "bounces", "world_boxes", "world_tris", "world_insts", "light_boxes", "light_tris", "light_insts"]
+        names = ["extend", "shadow", "probe", "paths", "bounces", "extend_boxes", "extend_tris", "extend_insts", "light_boxes", "light_tris", "light_insts", "shadow_boxes", "shadow_tris", "shadow_insts"]
         return dict(accum=accum, accum_sq=sq, position=pos, id=ids, seconds=secs, counters={k: int(v) for k, v in zip(names, cnt)})
 
 

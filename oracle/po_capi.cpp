@@ -409,7 +409,7 @@ void po_rng_stream(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t n, u
 
 // ---- frame driver: main.rs:181-207 + accumulate.wgsl:20-23 ------------------------------------------------
 // accum[W*H*4] += (rgb, 1) per sample; position[W*H*4], id[W*H] as main.rs:204-206 (may be null).
-// counters[11] += extend, shadow, probe, paths, bounces, world{boxes,tris,insts}, lights{boxes,tris,insts}.
+// counters[14] += extend, shadow, probe, paths, bounces, extend{boxes,tris,insts}, lights{boxes,tris,insts}, shadow{boxes,tris,insts}.
 // Pixel-major scheduling (each pixel's samples in order on one thread): sums are bit-identical to running
 // `sample_count` successive frames.  Returns elapsed seconds of the per-pixel loop.
 double po_render(const po_scene* s, const float* cam_origin, const float* cam_target, float fov_deg, float aspect, uint32_t W, uint32_t H, uint32_t sample_begin,
@@ -454,6 +454,7 @@ double po_render(const po_scene* s, const float* cam_origin, const float* cam_ta
             counters[0] += rc.extend; counters[1] += rc.shadow; counters[2] += rc.probe; counters[3] += rc.paths; counters[4] += rc.bounces;
             counters[5] += rc.world.boxes; counters[6] += rc.world.tris; counters[7] += rc.world.insts;
             counters[8] += rc.lights.boxes; counters[9] += rc.lights.tris; counters[10] += rc.lights.insts;
+            counters[11] += rc.shadow_w.boxes; counters[12] += rc.shadow_w.tris; counters[13] += rc.shadow_w.insts;
         }
     return el;
 }

@@ -496,7 +496,8 @@ inline V3 env_bilinear(const EnvMap& e, float u, float v)
 struct RayCounters
 {
     uint64_t extend = 0, shadow = 0, probe = 0, paths = 0, bounces = 0;
-    Counters world;   // work of world-TLAS traversals (extend + shadow)
+    Counters world;   // work of world-TLAS closest-hit traversals (extend)
+    Counters shadow_w; // work of world-TLAS any-hit traversals (shadow)
     Counters lights;  // work of lights-TLAS probes
 };
 inline float mis_heuristic2(float f, float g) { return (f * f) / ((f * f) + (g * g)); }              // :22, HEURISTIC_POWER = 2
@@ -522,7 +523,7 @@ inline V3 estimate_direct_explicit(WyRand& rng, const Ray& in_ray, const HitInfo
     if (dot3(out.d, hi.normal) > 0.0f)
     {
         rc.shadow += 1;
-        if (!tlas_any_intersect(sc.world, sc.world_blases, out, (1.0f - EPSILON) * distance, &rc.world))
+        if (!tlas_any_intersect(sc.world, sc.world_blases, out, (1.0f - EPSILON) * distance, &rc.shadow_w))
         {
             BsdfPdf bp = mat_bsdf_pdf(mat, incoming, out.d, hi.normal, hi.front_facing);
             float sample_pdf = li.pdf / tri_area(light);
@@ -545,7 +546,7 @@ inline V3 estimate_direct_bsdf(WyRand& rng, const Ray& in_ray, const HitInfo& hi
         if (tlas_intersect(sc.lights, sc.light_blases, out, INF, &lh, &rc.lights))
         {
             rc.shadow += 1;
-            if (!tlas_any_intersect(sc.world, sc.world_blases, out, lh.hi.t * (1.0f - EPSILON), &rc.world))
+            if (!tlas_any_intersect(sc.world, sc.world_blases, out, lh.hi.t * (1.0f - EPSILON), &rc.shadow_w))
             {
                 BsdfPdf bp = mat_bsdf_pdf(mat, incoming, out.d, hi.normal, hi.front_facing);
                 if (bp.pdf > 0.0f)  // MIN_PDF = 0 (:10)

@@ -338,7 +338,8 @@ int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height)
     REQUIRE_DEVICE(ctx);
     if (width == 0 || height == 0 || (uint64_t)width * height >= (1ull << 31)) return ctx->fail(PTB_ERR_INVALID, "bad frame size");
     PTB_CUDA(ctx, cudaSetDevice(ctx->device));
-    if (!ctx->rs) ctx->rs = new RenderState();
+    const bool fresh = ctx->rs == nullptr;
+    if (fresh) ctx->rs = new RenderState();
     RenderState& rs = *ctx->rs;
     const uint32_t npix = width * height;
     const bool bound = rs.accum && rs.accum != rs.accum_own.p;
@@ -360,7 +361,7 @@ int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height)
     if (ctx->second_moment) PTB_CUDA(ctx, cudaMemsetAsync(rs.accum_sq.p, 0, (size_t)npix * 16, ctx->stream));
     PTB_CUDA(ctx, cudaMemsetAsync(rs.position.p, 0, (size_t)npix * 16, ctx->stream));
     PTB_CUDA(ctx, cudaMemsetAsync(rs.id.p, 0, (size_t)npix * 4, ctx->stream));
-    PTB_CUDA(ctx, cudaMemsetAsync(rs.counters.p, 0, sizeof(WfCounters), ctx->stream));
+    if (fresh) PTB_CUDA(ctx, cudaMemsetAsync(rs.counters.p, 0, sizeof(WfCounters), ctx->stream));  // statistics persist until ptb_reset_counters
     return PTB_OK;
 }
 
