@@ -154,8 +154,19 @@ def test_render_statistical_parity(ptb, po, scenes):
     tz = z[: H // 12 * 12, : W // 12 * 12].reshape(H // 12, 12, W // 12, 12).mean(axis=(1, 3)) * 12.0
     assert np.abs(tz).max() < 5.0                        # no spatially coherent bias: tile-mean z (scaled by sqrt(144)) < 5
     assert abs(g1.mean() - r1.mean()) / r1.mean() < 0.01 # whole-image mean within 1 % at 64 spp
-    rmse_g, rmse_r = np.sqrt(((g1 - hi) ** 2).mean()), np.sqrt(((r1 - hi) ** 2).mean())
-    assert abs(rmse_g - rmse_r) / rmse_r < 0.06          # equal RMSE against the high-spp reference image at equal spp
+    # equal RMSE against the high-spp reference image at equal spp.  The Cornell estimator is heavy-tailed (fireflies up to the
+    # per-sample clamp of integrator.rs:274), so RMSE at 64 spp scatters ~10 % from seed to seed on the oracle alone: compare the
+    # mean over K independent seeds on both sides, tolerance = 3 standard errors of the difference + 2 %.
+    K = 5
+    rm_g, rm_r = [np.sqrt(((g1 - hi) ** 2).mean())], [np.sqrt(((r1 - hi) ** 2).mean())]
+    for k in range(1, K):
+        ctx.frame_begin(W, H)
+        ctx.render(0, N, seed=1001 + 17 * k, max_bounces=sd.max_bounces)
+        rm_g.append(np.sqrt(((ctx.read_accum()[..., :3] / N - hi) ** 2).mean()))
+        rm_r.append(np.sqrt(((sc.render(width=W, height=H, sample_count=N, seed=2002 + 31 * k)["accum"][..., :3] / N - hi) ** 2).mean()))
+    rm_g, rm_r = np.array(rm_g, np.float64), np.array(rm_r, np.float64)
+    tol = 3.0 * np.sqrt(rm_g.var(ddof=1) / K + rm_r.var(ddof=1) / K) + 0.02 * rm_r.mean()
+    assert abs(rm_g.mean() - rm_r.mean()) < tol, (rm_g, rm_r, tol)
 
 
 def test_furnace_and_sample_partition(ptb, po, scenes):
