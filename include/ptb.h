@@ -168,11 +168,15 @@ int ptb_bind_accum(ptb_context* ctx, void* dptr, size_t bytes);
 int ptb_get_counters(ptb_context* ctx, uint64_t out[8]);
 int ptb_reset_counters(ptb_context* ctx);
 /* With profiling on, every kernel launch of ptb_render is bracketed by CUDA events on the context stream.
- * times_ms: [0] whole ptb_render call (always measured), [1] raygen/regenerate, [2] extend, [3] shade, [4] shadow,
- * [5] light probe, [6] accumulate/finalise, [7] queue bookkeeping; launches: same indices. */
+ * times_ms: [0] whole ptb_render call (always measured), [1] init, [2] extend (incl. finalise/accumulate/raygen of regenerated
+ * slots), [3] shade, [4] nee (shadow + light-probe rays), [5] tail (all stages, one launch), [6..7] reserved; launches: same indices. */
 int ptb_set_profiling(ptb_context* ctx, int enable);
 int ptb_get_timing(ptb_context* ctx, float times_ms[8], uint32_t launches[8]);
-/* Tunables (evidence switches for DESIGN.md's layout decisions): name in {"sort_materials","extend_kernel","block_threads","blocks_per_sm"}. */
+/* Active slots (paths in flight + slots awaiting regeneration) after each wavefront iteration of the last ptb_render (first 8192). */
+int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active, uint32_t* count);
+/* Tunables (evidence switches for DESIGN.md's layout decisions): name in {"sort_materials","extend_kernel","block_threads",
+ * "blocks_per_sm","tail_threshold"}.  tail_threshold: active slots at which the wavefront loop hands the remaining slots to the
+ * single-launch tail kernel (< 0 automatic = half the resident thread capacity of that kernel, 0 = never). */
 int ptb_set_option(ptb_context* ctx, const char* name, int value);
 
 #ifdef __cplusplus

@@ -27,7 +27,7 @@ EXPORTS = [
     "ptb_light_count", "ptb_light_sampler", "ptb_bvh_stats", "ptb_trace_closest", "ptb_trace_any", "ptb_trace_upload", "ptb_trace_resident",
     "ptb_trace_download", "ptb_set_camera", "ptb_camera_rays", "ptb_ss_sobol", "ptb_rng_stream", "ptb_frame_begin", "ptb_render", "ptb_read_accum",
     "ptb_read_aux", "ptb_enable_second_moment", "ptb_read_second_moment", "ptb_accum_device_ptr", "ptb_bind_accum", "ptb_get_counters",
-    "ptb_reset_counters", "ptb_set_profiling", "ptb_get_timing", "ptb_set_option",
+    "ptb_reset_counters", "ptb_set_profiling", "ptb_get_timing", "ptb_get_iteration_log", "ptb_set_option",
 ]
 
 
@@ -289,8 +289,14 @@ class Context:
         t = np.zeros(8, np.float32)
         n = np.zeros(8, np.uint32)
         self._ck(self.L.ptb_get_timing(self.h, _p(t), _p(n)))
-        names = ["render", "regen", "extend", "shade", "shadow", "probe", "accumulate", "advance"]
+        names = ["render", "init", "extend", "shade", "nee", "tail", "reserved6", "reserved7"]
         return {k: (float(a), int(b)) for k, a, b in zip(names, t, n)}
+
+    def iteration_log(self, capacity=8192):
+        a = np.zeros(capacity, np.uint32)
+        n = C.c_uint32()
+        self._ck(self.L.ptb_get_iteration_log(self.h, capacity, _p(a), C.byref(n)))
+        return a[: n.value]
 
     def set_option(self, name, value):
         self._ck(self.L.ptb_set_option(self.h, name.encode(), int(value)))

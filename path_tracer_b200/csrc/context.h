@@ -80,6 +80,7 @@ struct ptb_context
     int opt_extend_kernel = 0;  // 0 wide, 1 reference-order
     int opt_block_threads = 128;
     int opt_blocks_per_sm = 8;
+    int opt_tail_threshold = -1;  // active slots at which ptb_render switches to the tail kernel (<0 automatic, 0 never)
     int profiling = 0;
     int second_moment = 0;
 

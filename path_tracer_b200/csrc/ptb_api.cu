@@ -427,6 +427,7 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "extend_kernel") ctx->opt_extend_kernel = value;
     else if (n == "block_threads") ctx->opt_block_threads = value;
     else if (n == "blocks_per_sm") ctx->opt_blocks_per_sm = value;
+    else if (n == "tail_threshold") ctx->opt_tail_threshold = value;
     else return ctx->fail(PTB_ERR_INVALID, "unknown option " + n);
     return PTB_OK;
 }

@@ -1,14 +1,19 @@
-// render.cu — the frame loop of main.rs:181-207 as wavefront kernels over SoA path state (wavefront.h holds the per-slot
-// bodies) plus the camera / jitter / RNG probes of the C ABI.
+// render.cu — the frame loop of main.rs:181-207 as wavefront kernels over per-slot path state (wavefront.h holds the
+// per-slot bodies) plus the camera / jitter / RNG probes of the C ABI.
 //
-// Kernels (all persistent: grid = SMs x blocks_per_sm, every warp pulls chunks of 32 queue entries from a cursor):
-//   k_regen   finalise + accumulate finished samples (single writer per pixel, no atomics) and raygen the next sample
-//   k_extend  closest hit on the world TLAS, then pushes the slot into the shade queue of its material kind
-//   k_shade   per-material queues processed kind by kind (a warp never mixes kinds); emits shadow / probe / next / term
-//   k_shadow  any-hit for explicit light samples
-//   k_probe   lights-TLAS closest hit + world any-hit for BSDF-sampled direct light
-//   k_advance 1 thread: swaps queue counts, folds ray statistics, resets cursors
-// Compaction between stages is a warp ballot + one atomicAdd per warp and queue.
+// One wavefront iteration = three persistent kernels (grid = SMs x blocks_per_sm; every warp pulls chunks of 32 queue
+// entries from a cursor):
+//   k_extend  (a) continuing paths: closest hit on the world TLAS; (b) slots whose path ended in the previous iteration:
+//             finalise + accumulate the finished sample (single writer per pixel, no atomics), raygen the next sample
+//             and trace its primary ray in the same thread.  Pushes the slot into the shade queue of its material kind.
+//   k_shade   per-material queues processed kind by kind (a warp never mixes kinds); emits shadow / probe entries and
+//             the continue / terminated queues of the next iteration
+//   k_nee     both direct-light estimates of a bounce in one thread: any-hit for the explicit light sample, lights-TLAS
+//             closest hit + world any-hit for the BSDF-sampled one; one read-modify-write of the slot's radiance
+// Queue counters live in three rotating sets (iteration it consumes set it%3, fills set (it+1)%3 and clears set (it+2)%3),
+// so no separate bookkeeping launch is needed.  Compaction between stages is warp ballot / match + one atomicAdd per warp
+// and queue.  When few paths remain (the tail of 1024-bounce paths) a single k_tail launch runs every remaining
+// slot to completion, one thread per slot, instead of thousands of near-empty iterations.
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -19,36 +24,46 @@
 
 namespace ptb {
 
+struct WfSet  // 64 B
+{
+    uint32_t n_cont, n_term;  // consumed by k_extend (polled by the host: keep first)
+    uint32_t n_nee, pad0;
+    uint32_t n_mat[8];
+    uint32_t cur_extend, cur_shade, cur_nee, pad;
+};
 struct WfCounters
 {
-    uint32_t n_ext, n_next, n_shadow, n_probe, n_term, pad0;
-    uint32_t n_mat[8];
-    uint32_t cur_regen, cur_extend, cur_shade, cur_shadow, cur_probe, pad1;
-    unsigned long long stat_extend, stat_shadow, stat_probe, stat_paths, stat_iters, stat_primary, stat_probe_shadow;
+    WfSet set[3];
+    unsigned long long stat_extend, stat_shadow, stat_probe, stat_paths, stat_iters, stat_probe_shadow;
 };
 
 struct Queues
 {
-    uint32_t* ext;   // current extend queue
-    uint32_t* next;  // extend queue being filled for the next iteration
-    uint32_t* mat;   // 7 queues of npix entries each
-    uint32_t* shadow;
-    uint32_t* probe;
-    uint32_t* term;
+    uint32_t* cont[2];  // continuing paths, double-buffered by iteration parity
+    uint32_t* term[2];  // slots whose path ended (to be finalised / regenerated)
+    uint32_t* mat;      // 7 queues of npix entries each
+    uint32_t* nee;      // slot | NEE_SHADOW_BIT | NEE_PROBE_BIT
     uint32_t npix;
     WfCounters* c;
 };
 
+constexpr uint32_t POLL_RING = 8192;
+
 struct RenderState
 {
     uint32_t W = 0, H = 0, npix = 0;
-    DBuf<float4> accum_own, accum_sq, position, ray_o, ray_d, weight, radiance, hit_tn, nee_o, sh_d, sh_c, pr_d, pr_f;
-    DBuf<uint32_t> id, hit_info, q_a, q_b, q_mat, q_shadow, q_probe, q_term;
-    DBuf<uint2> rng;
+    DBuf<float4> accum_own, accum_sq, position;
+    DBuf<RayRec> ray;
+    DBuf<PathRec> path;
+    DBuf<HitRec> hit;
+    DBuf<ShadowRec> shadow;
+    DBuf<ProbeRec> probe;
+    DBuf<uint32_t> id, q_cont0, q_cont1, q_term0, q_term1, q_mat, q_nee;
     DBuf<unsigned long long> volset;
     DBuf<WfCounters> counters;
     float4* accum = nullptr;  // bound or own
-    uint32_t* h_flags = nullptr;  // pinned
+    uint32_t* h_flags = nullptr;  // pinned, POLL_RING x 2
+    uint32_t log_iters = 0;       // iterations recorded in h_flags by the last ptb_render
     std::vector<cudaEvent_t> poll_events;
     std::vector<cudaEvent_t> prof_events;
     // host-side statistics
@@ -57,6 +72,7 @@ struct RenderState
     float t_class_ms[8] = {0};
     uint32_t n_class[8] = {0};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    int tail_capacity = -1;  // resident threads of k_tail on this device
 };
 
 // ---- device helpers ------------------------------------------------------------------------------------------------------
@@ -71,78 +87,102 @@ __device__ __forceinline__ void warp_push(uint32_t* q, uint32_t* counter, bool p
     base = __shfl_sync(0xffffffffu, base, leader);
     if (pred) q[base + __popc(m & ((1u << lane) - 1u))] = value;
 }
-__device__ __forceinline__ bool fetch_chunk(uint32_t* cursor, uint32_t n, uint32_t* base_out)
+// push into one of several queues selected per lane (key < 8; key == 0xff: no push): one atomicAdd per distinct key
+__device__ __forceinline__ void warp_push_keyed(uint32_t* q, size_t stride, uint32_t* counters, uint32_t key, uint32_t value)
 {
+    const unsigned grp = __match_any_sync(0xffffffffu, key);
+    const unsigned lane = threadIdx.x & 31u;
+    const int leader = __ffs((int)grp) - 1;
     uint32_t base = 0;
-    if ((threadIdx.x & 31u) == 0u) base = atomicAdd(cursor, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    *base_out = base;
-    return base < n;
+    if ((int)lane == leader && key != 0xffu) base = atomicAdd(counters + key, (uint32_t)__popc(grp));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (key != 0xffu) q[(size_t)key * stride + base + __popc(grp & ((1u << lane) - 1u))] = value;
+}
+__device__ __forceinline__ bool fetch_chunk(uint32_t* cursor, uint32_t nchunks, uint32_t* chunk_out)
+{
+    uint32_t c = 0;
+    if ((threadIdx.x & 31u) == 0u) c = atomicAdd(cursor, 1u);
+    c = __shfl_sync(0xffffffffu, c, 0);
+    *chunk_out = c;
+    return c < nchunks;
 }
 
 __global__ void __launch_bounds__(128) k_init(RenderView V, Queues Q)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= Q.npix) return;
-    V.ray_o[i].w = 0.0f;  // no sample in flight
-    V.ray_d[i].w = 0.0f;  // samples started = 0
-    Q.term[i] = i;
+    V.ray[i].o.w = 0.0f;  // no sample in flight
+    V.ray[i].d.w = 0.0f;  // samples started = 0
+    Q.term[0][i] = i;
     if (i == 0)
     {
-        Q.c->n_term = Q.npix;
-        Q.c->n_ext = Q.c->n_next = Q.c->n_shadow = Q.c->n_probe = 0;
-        for (int k = 0; k < 8; ++k) Q.c->n_mat[k] = 0;
-        Q.c->cur_regen = Q.c->cur_extend = Q.c->cur_shade = Q.c->cur_shadow = Q.c->cur_probe = 0;
+        for (int s = 0; s < 3; ++s) Q.c->set[s] = WfSet{};
+        Q.c->set[0].n_term = Q.npix;
     }
 }
 
-__global__ void __launch_bounds__(128) k_regen(RenderView V, Queues Q)
+template <bool SORT, bool BIN>
+__global__ void __launch_bounds__(128) k_extend(RenderView V, Queues Q, uint32_t it)
 {
-    const uint32_t n = Q.c->n_term;
-    const uint32_t lane = threadIdx.x & 31u;
-    uint32_t base;
-    while (fetch_chunk(&Q.c->cur_regen, n, &base))
+    WfSet& S = Q.c->set[it % 3u];
+    const uint32_t b = it & 1u;
+    const uint32_t n_cont = S.n_cont, n_term = S.n_term;
+    if (blockIdx.x == 0 && threadIdx.x == 0)
     {
-        const uint32_t i = base + lane;
-        const bool valid = i < n;
-        const uint32_t slot = valid ? Q.term[i] : 0u;
-        const uint32_t flags = valid ? regen_slot(V, slot) : 0u;
-        warp_push(Q.next, &Q.c->n_next, (flags & WF_NEXT) != 0u, slot);
-        const unsigned m = __ballot_sync(0xffffffffu, (flags & WF_NEXT) != 0u);
-        if (lane == 0u && m) atomicAdd(&Q.c->stat_paths, (unsigned long long)__popc(m));
+        Q.c->set[(it + 2u) % 3u] = WfSet{};  // consumed in iteration it-1, refilled from iteration it+1 on
+        if (n_cont + n_term) Q.c->stat_iters += 1;
     }
-}
-
-template <bool SORT>
-__global__ void __launch_bounds__(128) k_extend(RenderView V, Queues Q)
-{
-    const uint32_t n = Q.c->n_ext;
+    const uint32_t nc_c = (n_cont + 31u) >> 5, nc_t = (n_term + 31u) >> 5;
     const uint32_t lane = threadIdx.x & 31u;
-    uint32_t base;
-    while (fetch_chunk(&Q.c->cur_extend, n, &base))
+    uint32_t c;
+    while (fetch_chunk(&S.cur_extend, nc_c + nc_t, &c))
     {
-        const uint32_t i = base + lane;
-        const bool valid = i < n;
-        const uint32_t slot = valid ? Q.ext[i] : 0u;
-        uint32_t kind = valid ? extend_slot(V, slot) : 0xffu;
+        uint32_t slot = 0;
+        bool valid;
+        V3 o = ex::v3(0, 0, 0), d = ex::v3(0, 0, 1);
+        if (c < nc_c)
+        {
+            const uint32_t i = c * 32u + lane;
+            valid = i < n_cont;
+            if (valid)
+            {
+                slot = Q.cont[b][i];
+                const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
+                o = ex::v3(o4.x, o4.y, o4.z);
+                d = ex::v3(d4.x, d4.y, d4.z);
+            }
+        }
+        else
+        {
+            const uint32_t i = (c - nc_c) * 32u + lane;
+            valid = i < n_term;
+            if (valid)
+            {
+                slot = Q.term[b][i];
+                valid = (regen_slot(V, slot, &o, &d) & WF_NEXT) != 0u;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, valid);
+            if (lane == 0u && m) atomicAdd(&Q.c->stat_paths, (unsigned long long)__popc(m));
+        }
+        uint32_t kind = valid ? extend_ray_t<BIN>(V, slot, o, d) : 0xffu;
         if (!SORT && valid) kind = 0u;
-#pragma unroll
-        for (uint32_t k = 0; k < (SORT ? 7u : 1u); ++k) warp_push(Q.mat + (size_t)k * Q.npix, &Q.c->n_mat[k], kind == k, slot);
+        warp_push_keyed(Q.mat, Q.npix, S.n_mat, kind, slot);
     }
 }
 
-__global__ void __launch_bounds__(128) k_shade(RenderView V, Queues Q)
+__global__ void __launch_bounds__(128) k_shade(RenderView V, Queues Q, uint32_t it)
 {
+    WfSet& S = Q.c->set[it % 3u];
+    WfSet& N = Q.c->set[(it + 1u) % 3u];
+    const uint32_t nb = (it + 1u) & 1u;
     const uint32_t lane = threadIdx.x & 31u;
-    uint32_t cnt[7], chunks = 0;
+    uint32_t cnt[7], chunks = 0, total = 0;
 #pragma unroll
-    for (int k = 0; k < 7; ++k) { cnt[k] = Q.c->n_mat[k]; chunks += (cnt[k] + 31u) >> 5; }
-    for (;;)
+    for (int k = 0; k < 7; ++k) { cnt[k] = S.n_mat[k]; chunks += (cnt[k] + 31u) >> 5; total += cnt[k]; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) Q.c->stat_extend += total;
+    uint32_t c;
+    while (fetch_chunk(&S.cur_shade, chunks, &c))
     {
-        uint32_t c = 0;
-        if (lane == 0u) c = atomicAdd(&Q.c->cur_shade, 1u);
-        c = __shfl_sync(0xffffffffu, c, 0);
-        if (c >= chunks) break;
         uint32_t kind = 0, first = c;
 #pragma unroll
         for (int k = 0; k < 7; ++k)
@@ -154,51 +194,82 @@ __global__ void __launch_bounds__(128) k_shade(RenderView V, Queues Q)
         const bool valid = i < cnt[kind];
         const uint32_t slot = valid ? Q.mat[(size_t)kind * Q.npix + i] : 0u;
         const uint32_t flags = valid ? shade_slot(V, slot) : 0u;
-        warp_push(Q.shadow, &Q.c->n_shadow, (flags & WF_SHADOW) != 0u, slot);
-        warp_push(Q.probe, &Q.c->n_probe, (flags & WF_PROBE) != 0u, slot);
-        warp_push(Q.next, &Q.c->n_next, (flags & WF_NEXT) != 0u, slot);
-        warp_push(Q.term, &Q.c->n_term, (flags & WF_TERM) != 0u, slot);
+        warp_push(Q.nee, &S.n_nee, (flags & (WF_SHADOW | WF_PROBE)) != 0u, slot | ((flags & WF_SHADOW) ? NEE_SHADOW_BIT : 0u) | ((flags & WF_PROBE) ? NEE_PROBE_BIT : 0u));
+        warp_push(Q.cont[nb], &N.n_cont, (flags & WF_NEXT) != 0u, slot);
+        warp_push(Q.term[nb], &N.n_term, (flags & WF_TERM) != 0u, slot);
     }
 }
 
-__global__ void __launch_bounds__(128) k_shadow(RenderView V, Queues Q)
+template <bool BIN>
+__global__ void __launch_bounds__(128) k_nee(RenderView V, Queues Q, uint32_t it)
 {
-    const uint32_t n = Q.c->n_shadow;
+    WfSet& S = Q.c->set[it % 3u];
+    const uint32_t n = S.n_nee;
     const uint32_t lane = threadIdx.x & 31u;
-    uint32_t base;
-    while (fetch_chunk(&Q.c->cur_shadow, n, &base))
+    uint32_t c;
+    while (fetch_chunk(&S.cur_nee, (n + 31u) >> 5, &c))
     {
-        const uint32_t i = base + lane;
-        if (i < n) shadow_slot(V, Q.shadow[i]);
+        const uint32_t i = c * 32u + lane;
+        const uint32_t e = i < n ? Q.nee[i] : 0u;
+        const uint32_t flags = ((e & NEE_SHADOW_BIT) ? WF_SHADOW : 0u) | ((e & NEE_PROBE_BIT) ? WF_PROBE : 0u);
+        const uint32_t traced = flags ? nee_slot_t<BIN>(V, e & NEE_SLOT_MASK, flags) : 0u;
+        const unsigned ms = __ballot_sync(0xffffffffu, (flags & WF_SHADOW) != 0u), mp = __ballot_sync(0xffffffffu, (flags & WF_PROBE) != 0u), mt = __ballot_sync(0xffffffffu, traced != 0u);
+        if (lane == 0u)
+        {
+            if (ms) atomicAdd(&Q.c->stat_shadow, (unsigned long long)__popc(ms));
+            if (mp) atomicAdd(&Q.c->stat_probe, (unsigned long long)__popc(mp));
+            if (mt) atomicAdd(&Q.c->stat_probe_shadow, (unsigned long long)__popc(mt));
+        }
     }
 }
 
-__global__ void __launch_bounds__(128) k_probe(RenderView V, Queues Q)
+// The tail: one thread per remaining slot runs regen -> extend -> shade -> shadow -> probe until the slot has no samples left.
+template <bool BIN>
+__global__ void __launch_bounds__(64) k_tail(RenderView V, Queues Q, uint32_t it)
 {
-    const uint32_t n = Q.c->n_probe;
-    const uint32_t lane = threadIdx.x & 31u;
-    uint32_t base;
-    while (fetch_chunk(&Q.c->cur_probe, n, &base))
+    WfSet& S = Q.c->set[it % 3u];
+    const uint32_t b = it & 1u;
+    const uint32_t n_cont = S.n_cont, n_term = S.n_term;
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long n_ext = 0, n_sh = 0, n_pr = 0, n_ps = 0, n_paths = 0;
+    if (idx < n_cont + n_term)
     {
-        const uint32_t i = base + lane;
-        const uint32_t traced = (i < n) ? probe_slot(V, Q.probe[i]) : 0u;
-        const unsigned m = __ballot_sync(0xffffffffu, traced != 0u);
-        if (lane == 0u && m) atomicAdd(&Q.c->stat_probe_shadow, (unsigned long long)__popc(m));
+        const uint32_t slot = idx < n_cont ? Q.cont[b][idx] : Q.term[b][idx - n_cont];
+        bool need_regen = idx >= n_cont;
+        for (;;)
+        {
+            V3 o, d;
+            if (need_regen)
+            {
+                if (!(regen_slot(V, slot, &o, &d) & WF_NEXT)) break;
+                ++n_paths;
+            }
+            else
+            {
+                const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
+                o = ex::v3(o4.x, o4.y, o4.z);
+                d = ex::v3(d4.x, d4.y, d4.z);
+            }
+            extend_ray_t<BIN>(V, slot, o, d);
+            ++n_ext;
+            const uint32_t flags = shade_slot(V, slot);
+            if (flags & (WF_SHADOW | WF_PROBE))
+            {
+                n_ps += nee_slot_t<BIN>(V, slot, flags);
+                n_sh += (flags & WF_SHADOW) ? 1u : 0u;
+                n_pr += (flags & WF_PROBE) ? 1u : 0u;
+            }
+            need_regen = (flags & WF_TERM) != 0u;
+        }
     }
-}
-
-// end of an iteration (1 thread): fold statistics, make q_next current, reset counts and cursors
-__global__ void k_advance(Queues Q)
-{
-    WfCounters& c = *Q.c;
-    c.stat_extend += c.n_ext;
-    c.stat_shadow += c.n_shadow;
-    c.stat_probe += c.n_probe;
-    c.stat_iters += 1;
-    c.n_ext = c.n_next;
-    c.n_next = c.n_term = c.n_shadow = c.n_probe = 0;
-    for (int k = 0; k < 8; ++k) c.n_mat[k] = 0;
-    c.cur_regen = c.cur_extend = c.cur_shade = c.cur_shadow = c.cur_probe = 0;
+    if (n_ext | n_paths)
+    {
+        atomicAdd(&Q.c->stat_extend, n_ext);
+        atomicAdd(&Q.c->stat_shadow, n_sh);
+        atomicAdd(&Q.c->stat_probe, n_pr);
+        atomicAdd(&Q.c->stat_probe_shadow, n_ps);
+        atomicAdd(&Q.c->stat_paths, n_paths);
+    }
 }
 
 // ---- probes (device code of raygen, run on small batches) -------------------------------------------------------------------
@@ -233,11 +304,10 @@ void render_state_destroy(ptb_context* ctx)
     if (rs->ev_begin) cudaEventDestroy(rs->ev_begin);
     if (rs->ev_end) cudaEventDestroy(rs->ev_end);
     if (rs->h_flags) cudaFreeHost(rs->h_flags);
-    DBuf<float4>* f4s[] = {&rs->accum_own, &rs->accum_sq, &rs->position, &rs->ray_o, &rs->ray_d, &rs->weight, &rs->radiance, &rs->hit_tn, &rs->nee_o, &rs->sh_d, &rs->sh_c, &rs->pr_d, &rs->pr_f};
-    for (auto* b : f4s) b->release();
-    DBuf<uint32_t>* u32s[] = {&rs->id, &rs->hit_info, &rs->q_a, &rs->q_b, &rs->q_mat, &rs->q_shadow, &rs->q_probe, &rs->q_term};
+    rs->accum_own.release(); rs->accum_sq.release(); rs->position.release();
+    rs->ray.release(); rs->path.release(); rs->hit.release(); rs->shadow.release(); rs->probe.release();
+    DBuf<uint32_t>* u32s[] = {&rs->id, &rs->q_cont0, &rs->q_cont1, &rs->q_term0, &rs->q_term1, &rs->q_mat, &rs->q_nee};
     for (auto* b : u32s) b->release();
-    rs->rng.release();
     rs->volset.release();
     rs->counters.release();
     delete rs;
@@ -336,7 +406,7 @@ int ptb_enable_second_moment(ptb_context* ctx, int enable)
 int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height)
 {
     REQUIRE_DEVICE(ctx);
-    if (width == 0 || height == 0 || (uint64_t)width * height >= (1ull << 31)) return ctx->fail(PTB_ERR_INVALID, "bad frame size");
+    if (width == 0 || height == 0 || (uint64_t)width * height > (uint64_t)NEE_SLOT_MASK) return ctx->fail(PTB_ERR_INVALID, "bad frame size");
     PTB_CUDA(ctx, cudaSetDevice(ctx->device));
     const bool fresh = ctx->rs == nullptr;
     if (fresh) ctx->rs = new RenderState();
@@ -345,16 +415,20 @@ int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height)
     const bool bound = rs.accum && rs.accum != rs.accum_own.p;
     if (bound && npix != rs.npix) return ctx->fail(PTB_ERR_INVALID, "bound accumulation buffer has a different size; rebind it");
     rs.W = width; rs.H = height; rs.npix = npix;
-    DBuf<float4>* f4s[] = {&rs.accum_own, &rs.position, &rs.ray_o, &rs.ray_d, &rs.weight, &rs.radiance, &rs.hit_tn, &rs.nee_o, &rs.sh_d, &rs.sh_c, &rs.pr_d, &rs.pr_f};
-    for (auto* b : f4s) PTB_CUDA(ctx, b->resize(npix));
+    PTB_CUDA(ctx, rs.accum_own.resize(npix));
+    PTB_CUDA(ctx, rs.position.resize(npix));
+    PTB_CUDA(ctx, rs.ray.resize(npix));
+    PTB_CUDA(ctx, rs.path.resize(npix));
+    PTB_CUDA(ctx, rs.hit.resize(npix));
+    PTB_CUDA(ctx, rs.shadow.resize(npix));
+    PTB_CUDA(ctx, rs.probe.resize(npix));
     if (ctx->second_moment) PTB_CUDA(ctx, rs.accum_sq.resize(npix));
-    DBuf<uint32_t>* u32s[] = {&rs.id, &rs.hit_info, &rs.q_a, &rs.q_b, &rs.q_shadow, &rs.q_probe, &rs.q_term};
+    DBuf<uint32_t>* u32s[] = {&rs.id, &rs.q_cont0, &rs.q_cont1, &rs.q_term0, &rs.q_term1, &rs.q_nee};
     for (auto* b : u32s) PTB_CUDA(ctx, b->resize(npix));
     PTB_CUDA(ctx, rs.q_mat.resize((size_t)npix * 7));
-    PTB_CUDA(ctx, rs.rng.resize(npix));
     PTB_CUDA(ctx, rs.volset.resize(npix));
     PTB_CUDA(ctx, rs.counters.resize(1));
-    if (!rs.h_flags) PTB_CUDA(ctx, cudaHostAlloc((void**)&rs.h_flags, 256 * sizeof(uint32_t), cudaHostAllocDefault));
+    if (!rs.h_flags) PTB_CUDA(ctx, cudaHostAlloc((void**)&rs.h_flags, POLL_RING * 2 * sizeof(uint32_t), cudaHostAllocDefault));
     if (!rs.ev_begin) { PTB_CUDA(ctx, cudaEventCreate(&rs.ev_begin)); PTB_CUDA(ctx, cudaEventCreate(&rs.ev_end)); }
     if (!bound) rs.accum = rs.accum_own.p;
     PTB_CUDA(ctx, cudaMemsetAsync(rs.accum, 0, (size_t)npix * 16, ctx->stream));
@@ -407,11 +481,11 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     V.accum = rs.accum;
     V.accum_sq = ctx->second_moment ? rs.accum_sq.p : nullptr;
     V.position = rs.position.p; V.id = rs.id.p;
-    V.ray_o = rs.ray_o.p; V.ray_d = rs.ray_d.p; V.weight = rs.weight.p; V.radiance = rs.radiance.p; V.rng = rs.rng.p;
+    V.ray = rs.ray.p; V.path = rs.path.p; V.hit = rs.hit.p; V.shadow = rs.shadow.p; V.probe = rs.probe.p;
     V.volset = ctx->scene.volumes.empty() ? nullptr : rs.volset.p;
-    V.hit_tn = rs.hit_tn.p; V.hit_info = rs.hit_info.p; V.nee_o = rs.nee_o.p; V.sh_d = rs.sh_d.p; V.sh_c = rs.sh_c.p; V.pr_d = rs.pr_d.p; V.pr_f = rs.pr_f.p;
     Queues Q{};
-    Q.ext = rs.q_a.p; Q.next = rs.q_b.p; Q.mat = rs.q_mat.p; Q.shadow = rs.q_shadow.p; Q.probe = rs.q_probe.p; Q.term = rs.q_term.p;
+    Q.cont[0] = rs.q_cont0.p; Q.cont[1] = rs.q_cont1.p; Q.term[0] = rs.q_term0.p; Q.term[1] = rs.q_term1.p;
+    Q.mat = rs.q_mat.p; Q.nee = rs.q_nee.p;
     Q.npix = rs.npix;
     Q.c = rs.counters.p;
 
@@ -433,58 +507,66 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         prof_class.push_back(cls);
         return cudaEventRecord(rs.prof_events[prof_used++], st);
     };
-    while (rs.poll_events.size() < 64)
+    const uint32_t NEV = 64;
+    while (rs.poll_events.size() < NEV)
     {
         cudaEvent_t e;
         PTB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         rs.poll_events.push_back(e);
     }
+    if (rs.tail_capacity < 0)
+    {
+        int per_sm = 0;
+        PTB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tail<false>, 64, 0));
+        rs.tail_capacity = per_sm * 64 * ctx->sm_count;
+    }
+    // switch to the tail kernel once every remaining slot fits on the device at once (0 disables, <0 = automatic)
+    const uint32_t tail_threshold = ctx->opt_tail_threshold < 0 ? (uint32_t)rs.tail_capacity / 2u : (uint32_t)ctx->opt_tail_threshold;
 
     PTB_CUDA(ctx, cudaEventRecord(rs.ev_begin, st));
     PTB_CUDA(ctx, mark(-1));
     k_init<<<(rs.npix + threads - 1) / threads, threads, 0, st>>>(V, Q);
-    // first regen fills q_next from q_term = all slots
-    Q.next = rs.q_a.p;  // the very first extend queue
-    k_regen<<<grid, threads, 0, st>>>(V, Q);
     PTB_CUDA(ctx, mark(1));
-    k_advance<<<1, 1, 0, st>>>(Q);
-    PTB_CUDA(ctx, mark(7));
-    rs.launches += 3;
-    uint32_t* cur = rs.q_a.p;
-    uint32_t* other = rs.q_b.p;
-    const bool sort = ctx->opt_sort_materials != 0;
+    rs.launches += 1;
+    const bool sort = ctx->opt_sort_materials != 0, bin = V.extend_kernel != 0u;
     const uint32_t LAG = 8;
+    rs.log_iters = 0;
     for (uint32_t it = 0;; ++it)
     {
-        Q.ext = cur;
-        Q.next = other;
-        if (sort) k_extend<true><<<grid, threads, 0, st>>>(V, Q);
-        else k_extend<false><<<grid, threads, 0, st>>>(V, Q);
+        if (bin) k_extend<true, true><<<grid, threads, 0, st>>>(V, Q, it);
+        else if (sort) k_extend<true, false><<<grid, threads, 0, st>>>(V, Q, it);
+        else k_extend<false, false><<<grid, threads, 0, st>>>(V, Q, it);
         PTB_CUDA(ctx, mark(2));
-        k_shade<<<grid, threads, 0, st>>>(V, Q);
+        k_shade<<<grid, threads, 0, st>>>(V, Q, it);
         PTB_CUDA(ctx, mark(3));
+        rs.launches += 2;
         if (V.enable_nee)
         {
-            k_shadow<<<grid, threads, 0, st>>>(V, Q);
+            if (bin) k_nee<true><<<grid, threads, 0, st>>>(V, Q, it);
+            else k_nee<false><<<grid, threads, 0, st>>>(V, Q, it);
             PTB_CUDA(ctx, mark(4));
-            k_probe<<<grid, threads, 0, st>>>(V, Q);
-            PTB_CUDA(ctx, mark(5));
-            rs.launches += 2;
+            rs.launches += 1;
         }
-        k_regen<<<grid, threads, 0, st>>>(V, Q);
-        PTB_CUDA(ctx, mark(1));
-        k_advance<<<1, 1, 0, st>>>(Q);
-        PTB_CUDA(ctx, mark(7));
-        rs.launches += 4;
         PTB_CUDA(ctx, cudaGetLastError());
-        std::swap(cur, other);
-        // termination poll, LAG iterations behind the launch front
-        PTB_CUDA(ctx, cudaMemcpyAsync(&rs.h_flags[it % 64], &rs.counters.p->n_ext, 4, cudaMemcpyDeviceToHost, st));
-        PTB_CUDA(ctx, cudaEventRecord(rs.poll_events[it % 64], st));
+        // active-slot count of the next iteration, read LAG iterations behind the launch front
+        PTB_CUDA(ctx, cudaMemcpyAsync(&rs.h_flags[(it % POLL_RING) * 2], &rs.counters.p->set[(it + 1u) % 3u].n_cont, 8, cudaMemcpyDeviceToHost, st));
+        PTB_CUDA(ctx, cudaEventRecord(rs.poll_events[it % NEV], st));
+        rs.log_iters = it + 1;
         if (it >= LAG)
         {
-            PTB_CUDA(ctx, cudaEventSynchronize(rs.poll_events[(it - LAG) % 64]));
-            if (rs.h_flags[(it - LAG) % 64] == 0u) break;
+            PTB_CUDA(ctx, cudaEventSynchronize(rs.poll_events[(it - LAG) % NEV]));
+            const uint32_t* f = &rs.h_flags[((it - LAG) % POLL_RING) * 2];
+            const uint32_t active = f[0] + f[1];
+            if (active == 0u) break;
+            if (active <= tail_threshold)
+            {
+                if (bin) k_tail<true><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);
+                else k_tail<false><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);  // active counts never grow: `active` bounds the queue at it+1
+                PTB_CUDA(ctx, mark(5));
+                PTB_CUDA(ctx, cudaGetLastError());
+                rs.launches += 1;
+                break;
+            }
         }
     }
     PTB_CUDA(ctx, cudaEventRecord(rs.ev_end, st));
@@ -504,6 +586,17 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             if (cls >= 1 && cls < 8) { rs.t_class_ms[cls] += d; rs.n_class[cls] += 1; }
         }
     }
+    return PTB_OK;
+}
+
+int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active, uint32_t* count)
+{
+    REQUIRE_DEVICE(ctx);
+    if (!ctx->rs || !count) return ctx->fail(PTB_ERR_INVALID, "no frame");
+    const uint32_t n = std::min<uint32_t>(std::min<uint32_t>(ctx->rs->log_iters, POLL_RING), capacity);
+    PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (uint32_t i = 0; i < n && active; ++i) active[i] = ctx->rs->h_flags[i * 2] + ctx->rs->h_flags[i * 2 + 1];
+    *count = n;
     return PTB_OK;
 }
 

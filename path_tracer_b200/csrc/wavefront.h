@@ -1,5 +1,5 @@
 // wavefront.h — the per-slot bodies of the wavefront stages (host+device), restating integrate() (integrator.rs:143-281)
-// and the frame loop (main.rs:181-207) as a state machine over SoA path state:
+// and the frame loop (main.rs:181-207) as a state machine over per-slot path state:
 //
 //   regen  : finish the previous sample of a slot (integrator.rs:272-280, accumulate.wgsl:23) and start the next one
 //            (main.rs:187-199: seed draw, Sobol jitter, Camera::create_ray)
@@ -12,12 +12,43 @@
 // One slot == one pixel; a slot runs its pixel's samples back to back (path regeneration), so accum[pixel] has a single
 // writer and needs no atomics.  Queues between stages are handled by the callers (render.cu on the device, warp-aggregated;
 // tests/hostemu sequentially on the host): the bodies only return flags.
+//
+// Path state lives in HBM as 32-byte records (one DRAM sector each, two 128-bit accesses): a stage that touches a record
+// uses the whole sector, whatever order the queue presents the slots in.
 #pragma once
 #include "../../include/ptb.h"
 #include "shading.h"
 #include "traverse.h"
 
 namespace ptb {
+
+struct alignas(32) RayRec     // current ray of the path (ray.rs:1-8 without inv_direction, which is recomputed)
+{
+    float4 o;  // origin.xyz, w = bits: bounce (low 24) | last_delta << 24 | has_sample << 25
+    float4 d;  // direction.xyz, w = bits: samples started so far in this ptb_render call
+};
+struct alignas(32) PathRec    // integrator.rs:153-154
+{
+    float4 weight;    // path_weight.xyz
+    float4 radiance;  // accumulated.xyz
+};
+struct alignas(32) HitRec     // HitInfo (model.rs:5-11) as the shade stage needs it + the path's RNG state
+{
+    float4 tn;        // t, world-space ray-facing normal.xyz
+    uint32_t info;    // InstanceRow index | front_facing << 31 ; 0xffffffff = miss
+    uint32_t rng_lo, rng_hi;
+    uint32_t pad;
+};
+struct alignas(32) ShadowRec  // explicit light sample awaiting its visibility test (integrator.rs:56)
+{
+    float4 d;  // direction.xyz, w = t_max
+    float4 c;  // contribution if unoccluded
+};
+struct alignas(32) ProbeRec   // BSDF-sampled light direction awaiting lights-TLAS probe + visibility (integrator.rs:100-103)
+{
+    float4 d;  // direction.xyz, w = bsdf pdf
+    float4 f;  // path_weight * weakening * bsdf / pdf
+};
 
 struct RenderView
 {
@@ -34,24 +65,18 @@ struct RenderView
     float4* accum_sq;  // optional
     float4* position;  // main.rs:205
     uint32_t* id;      // main.rs:206
-    // per slot
-    float4* ray_o;     // o.xyz, w = bits: bounce (low 24) | last_delta << 24 | has_sample << 25
-    float4* ray_d;     // d.xyz, w = bits: samples started so far
-    float4* weight;    // path_weight.xyz
-    float4* radiance;  // accumulated.xyz
-    uint2* rng;
+    // per slot (== pixel)
+    RayRec* ray;
+    PathRec* path;
+    HitRec* hit;
+    ShadowRec* shadow;  // origin of shadow and probe rays = ray[slot].o (the hit point, written by shade)
+    ProbeRec* probe;
     unsigned long long* volset;
-    float4* hit_tn;    // t, normal.xyz
-    uint32_t* hit_info;  // InstanceRow index | front << 31 ; 0xffffffff = miss
-    float4* nee_o;     // origin of this bounce's shadow and probe rays (the hit point)
-    float4* sh_d;      // shadow ray direction, w = t_max
-    float4* sh_c;      // contribution if unoccluded
-    float4* pr_d;      // probe direction, w = bsdf pdf
-    float4* pr_f;      // path_weight * weakening * bsdf / pdf
 };
 
 enum : uint32_t { WF_NEXT = 1u, WF_TERM = 2u, WF_SHADOW = 4u, WF_PROBE = 8u };
 constexpr uint32_t ST_LAST_DELTA = 1u << 24, ST_HAS_SAMPLE = 1u << 25, ST_BOUNCE_MASK = (1u << 24) - 1u;
+constexpr uint32_t NEE_SHADOW_BIT = 0x80000000u, NEE_PROBE_BIT = 0x40000000u, NEE_SLOT_MASK = 0x3fffffffu;  // nee queue entry = slot | flags
 constexpr uint32_t Q_MISS = 6;  // shade queue kinds: 0..5 = material kinds, 6 = miss
 
 PTB_HD float4 f4(float x, float y, float z, float w)
@@ -62,14 +87,16 @@ PTB_HD float4 f4(float x, float y, float z, float w)
 }
 
 // ---- regen ---------------------------------------------------------------------------------------------------------------
-PTB_HD uint32_t regen_slot(const RenderView& V, uint32_t slot)
+// Finalises the slot's finished sample (if any), then starts the next one; the camera ray is returned in registers (and
+// stored) so the caller can trace it right away.
+PTB_HD uint32_t regen_slot(const RenderView& V, uint32_t slot, V3* o_out, V3* d_out)
 {
-    const uint32_t state = ex::bits(V.ray_o[slot].w);
-    uint32_t started = ex::bits(V.ray_d[slot].w);
+    const uint32_t state = ex::bits(V.ray[slot].o.w);
+    uint32_t started = ex::bits(V.ray[slot].d.w);
     if (state & ST_HAS_SAMPLE)
     {
         // integrator.rs:272-280 then accumulate.wgsl:23
-        const float4 r4 = V.radiance[slot];
+        const float4 r4 = V.path[slot].radiance;
         V3 c = ex::v3(r4.x, r4.y, r4.z);
         if (finite3(c))
         {
@@ -89,7 +116,7 @@ PTB_HD uint32_t regen_slot(const RenderView& V, uint32_t slot)
     }
     if (started >= V.sample_count)
     {
-        V.ray_o[slot].w = ex::from_bits(0u);
+        V.ray[slot].o.w = ex::from_bits(0u);
         return 0u;
     }
     // main.rs:187-199
@@ -104,61 +131,71 @@ PTB_HD uint32_t regen_slot(const RenderView& V, uint32_t slot)
     const float u = ex::div(ex::add((float)x, jx), (float)V.W), v = ex::div(ex::add((float)y, jy), (float)V.H);
     V3 o, d;
     camera_ray(V.cam, u, v, &o, &d);
-    V.ray_o[slot] = f4(o.x, o.y, o.z, ex::from_bits(ST_HAS_SAMPLE));  // bounce 0, last_delta false
-    V.ray_d[slot] = f4(d.x, d.y, d.z, ex::from_bits(started + 1u));
-    V.weight[slot] = f4(1.0f, 1.0f, 1.0f, 0.0f);
-    V.radiance[slot] = f4(0.0f, 0.0f, 0.0f, 0.0f);
-    uint2 rs;
-    rs.x = (uint32_t)rng.s;
-    rs.y = (uint32_t)(rng.s >> 32);
-    V.rng[slot] = rs;
+    V.ray[slot].o = f4(o.x, o.y, o.z, ex::from_bits(ST_HAS_SAMPLE));  // bounce 0, last_delta false
+    V.ray[slot].d = f4(d.x, d.y, d.z, ex::from_bits(started + 1u));
+    V.path[slot].weight = f4(1.0f, 1.0f, 1.0f, 0.0f);
+    V.path[slot].radiance = f4(0.0f, 0.0f, 0.0f, 0.0f);
+    V.hit[slot].rng_lo = (uint32_t)rng.s;
+    V.hit[slot].rng_hi = (uint32_t)(rng.s >> 32);
     if (V.volset) V.volset[slot] = 0ull;
     // integrator.rs:156-157 defaults; overwritten at b == 0 on a hit
     const V3 far = ex::ray_at(o, d, 1e5f);
     V.position[slot] = f4(far.x, far.y, far.z, 1e5f);
     V.id[slot] = (V.id[slot] << 16) | 255u;  // main.rs:206 with first_id defaulting to u8::MAX (integrator.rs:157)
+    *o_out = o;
+    *d_out = d;
     return WF_NEXT;
+}
+PTB_HD uint32_t regen_slot(const RenderView& V, uint32_t slot)
+{
+    V3 o, d;
+    return regen_slot(V, slot, &o, &d);
 }
 
 // ---- extend --------------------------------------------------------------------------------------------------------------
 // returns the shade-queue kind (material kind of the hit BLAS, or Q_MISS)
-PTB_HD uint32_t extend_slot(const RenderView& V, uint32_t slot)
+template <bool BIN>
+PTB_HD uint32_t extend_ray_t(const RenderView& V, uint32_t slot, V3 o, V3 d)
 {
-    const float4 o4 = V.ray_o[slot], d4 = V.ray_d[slot];
-    const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
     Hit h;
     h.inst = 0xffffffffu;
-    const bool f = V.extend_kernel ? bin_traverse<false>(V.S, 0, o, d, ex::inf(), &h) : wide_traverse<false>(V.S, 0, o, d, ex::inf(), &h);
+    const bool f = BIN ? bin_traverse<false>(V.S, 0, o, d, ex::inf(), &h) : wide_traverse<false>(V.S, 0, o, d, ex::inf(), &h);
     if (!f)
     {
-        V.hit_info[slot] = 0xffffffffu;
+        V.hit[slot].info = 0xffffffffu;
         return Q_MISS;
     }
-    const uint32_t prim = V.extend_kernel ? h.slot_or_prim : V.S.tri_prim[h.slot_or_prim];
+    const uint32_t prim = BIN ? h.slot_or_prim : V.S.tri_prim[h.slot_or_prim];
     V3 n;
     bool ff;
     finish_hit(V.S, d, h.inst, prim, h.u, h.v, &n, &ff);
-    V.hit_tn[slot] = f4(h.t, n.x, n.y, n.z);
-    V.hit_info[slot] = h.inst | (ff ? 0x80000000u : 0u);
+    V.hit[slot].tn = f4(h.t, n.x, n.y, n.z);
+    V.hit[slot].info = h.inst | (ff ? 0x80000000u : 0u);
     return V.S.mat[V.S.inst[h.inst].blas].kind;
+}
+PTB_HD uint32_t extend_ray(const RenderView& V, uint32_t slot, V3 o, V3 d) { return V.extend_kernel ? extend_ray_t<true>(V, slot, o, d) : extend_ray_t<false>(V, slot, o, d); }
+PTB_HD uint32_t extend_slot(const RenderView& V, uint32_t slot)
+{
+    const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
+    return extend_ray(V, slot, ex::v3(o4.x, o4.y, o4.z), ex::v3(d4.x, d4.y, d4.z));
 }
 
 // ---- shade ---------------------------------------------------------------------------------------------------------------
 PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
 {
-    const float4 o4 = V.ray_o[slot], d4 = V.ray_d[slot];
+    const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
     const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
     uint32_t state = ex::bits(o4.w);
     const uint32_t b = state & ST_BOUNCE_MASK;
     const bool last_delta = (state & ST_LAST_DELTA) != 0u;
-    const uint32_t info = V.hit_info[slot];
-    const float4 w4 = V.weight[slot];
+    const uint32_t info = V.hit[slot].info;
+    const float4 w4 = V.path[slot].weight;
     V3 path_weight = ex::v3(w4.x, w4.y, w4.z);
 
     if (info == 0xffffffffu)
     {
         // miss: integrator.rs:254-269
-        const float4 r4 = V.radiance[slot];
+        const float4 r4 = V.path[slot].radiance;
         V3 acc = ex::v3(r4.x, r4.y, r4.z);
         if (V.S.env)
         {
@@ -167,20 +204,19 @@ PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
             acc = acc + env_bilinear(V.S.env, V.S.env_w, V.S.env_h, u, v) * path_weight;
         }
         else acc = acc + ex::v3(0.006f, 0.006f, 0.006f) * path_weight;
-        V.radiance[slot] = f4(acc.x, acc.y, acc.z, 0.0f);
+        V.path[slot].radiance = f4(acc.x, acc.y, acc.z, 0.0f);
         return WF_TERM;
     }
 
-    const float4 h4 = V.hit_tn[slot];
+    const float4 h4 = V.hit[slot].tn;
     const float t = h4.x;
     const V3 normal = ex::v3(h4.y, h4.z, h4.w);
     const bool front = (info & 0x80000000u) != 0u;
     const uint32_t inst = info & 0x7fffffffu;
     const uint32_t blas = V.S.inst[inst].blas;
     const Mat mat = load_mat(V.S.mat, blas);
-    const uint2 rs = V.rng[slot];
     Rng rng;
-    rng.s = (unsigned long long)rs.x | ((unsigned long long)rs.y << 32);
+    rng.s = (unsigned long long)V.hit[slot].rng_lo | ((unsigned long long)V.hit[slot].rng_hi << 32);
     const V3 hit_p = ex::ray_at(o, d, t);  // Ray::at (fused, ray.rs:20)
 
     if (b == 0u)  // integrator.rs:181-185
@@ -226,8 +262,8 @@ PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
         {
             if (!V.enable_nee || last_delta || b == 0u)
             {
-                const float4 r4 = V.radiance[slot];
-                V.radiance[slot] = f4(fmaf(mat.colour.x, path_weight.x, r4.x), fmaf(mat.colour.y, path_weight.y, r4.y), fmaf(mat.colour.z, path_weight.z, r4.z), 0.0f);
+                const float4 r4 = V.path[slot].radiance;
+                V.path[slot].radiance = f4(fmaf(mat.colour.x, path_weight.x, r4.x), fmaf(mat.colour.y, path_weight.y, r4.y), fmaf(mat.colour.z, path_weight.z, r4.z), 0.0f);
             }
             done = true;
         }
@@ -267,9 +303,8 @@ PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
                     const float wgt = (light_pdf * light_pdf) / (light_pdf * light_pdf + bp.pdf * bp.pdf);  // mis_heuristic<2>
                     const Mat lmat = load_mat(V.S.mat, L.blas);
                     const V3 c = path_weight * ((lmat.colour * wgt * weakening(mat.kind, ld, normal)) * bp.bsdf / light_pdf);
-                    V.nee_o[slot] = f4(hit_p.x, hit_p.y, hit_p.z, 0.0f);
-                    V.sh_d[slot] = f4(ld.x, ld.y, ld.z, (1.0f - ex::EPS) * dist);
-                    V.sh_c[slot] = f4(c.x, c.y, c.z, 0.0f);
+                    V.shadow[slot].d = f4(ld.x, ld.y, ld.z, (1.0f - ex::EPS) * dist);
+                    V.shadow[slot].c = f4(c.x, c.y, c.z, 0.0f);
                     flags |= WF_SHADOW;
                 }
                 // BSDF-sampled light (integrator.rs:77-130): the material's draws, always
@@ -280,9 +315,8 @@ PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
                     if (bp.pdf > 0.0f)  // MIN_PDF (checked upstream after the visibility tests; order is immaterial)
                     {
                         const V3 f = path_weight * (weakening(mat.kind, pd, normal) * bp.bsdf / bp.pdf);
-                        V.nee_o[slot] = f4(hit_p.x, hit_p.y, hit_p.z, 0.0f);
-                        V.pr_d[slot] = f4(pd.x, pd.y, pd.z, bp.pdf);
-                        V.pr_f[slot] = f4(f.x, f.y, f.z, 0.0f);
+                        V.probe[slot].d = f4(pd.x, pd.y, pd.z, bp.pdf);
+                        V.probe[slot].f = f4(f.x, f.y, f.z, 0.0f);
                         flags |= WF_PROBE;
                     }
                 }
@@ -313,48 +347,49 @@ PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
         if (!done)
         {
             state = (state & ~(ST_BOUNCE_MASK | ST_LAST_DELTA)) | nb | (new_last_delta ? ST_LAST_DELTA : 0u);
-            V.ray_o[slot] = f4(new_o.x, new_o.y, new_o.z, ex::from_bits(state));
-            V.ray_d[slot] = f4(new_d.x, new_d.y, new_d.z, d4.w);
-            V.weight[slot] = f4(path_weight.x, path_weight.y, path_weight.z, 0.0f);
-            uint2 ro;
-            ro.x = (uint32_t)rng.s;
-            ro.y = (uint32_t)(rng.s >> 32);
-            V.rng[slot] = ro;
+            V.ray[slot].o = f4(new_o.x, new_o.y, new_o.z, ex::from_bits(state));
+            V.ray[slot].d = f4(new_d.x, new_d.y, new_d.z, d4.w);
+            V.path[slot].weight = f4(path_weight.x, path_weight.y, path_weight.z, 0.0f);
+            V.hit[slot].rng_lo = (uint32_t)rng.s;
+            V.hit[slot].rng_hi = (uint32_t)(rng.s >> 32);
             return flags | WF_NEXT;
         }
     }
+    // the path ends here, but its last NEE rays still start at the hit point: keep it as the slot's ray origin (state bits unchanged)
+    if (flags & (WF_SHADOW | WF_PROBE)) V.ray[slot].o = f4(hit_p.x, hit_p.y, hit_p.z, o4.w);
     return flags | WF_TERM;
 }
 
 // ---- shadow --------------------------------------------------------------------------------------------------------------
-PTB_HD void shadow_slot(const RenderView& V, uint32_t slot)
+// adds the explicit light sample's contribution to *r when the shadow ray is unoccluded (integrator.rs:56-70)
+template <bool BIN>
+PTB_HD void shadow_contrib_t(const RenderView& V, uint32_t slot, V3 o, float4* r)
 {
-    const float4 o4 = V.nee_o[slot], d4 = V.sh_d[slot];
+    const float4 d4 = V.shadow[slot].d;
     Hit h;
-    const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
-    const bool occluded = V.extend_kernel ? bin_traverse<true>(V.S, 0, o, d, d4.w, &h) : wide_traverse<true>(V.S, 0, o, d, d4.w, &h);
+    const V3 d = ex::v3(d4.x, d4.y, d4.z);
+    const bool occluded = BIN ? bin_traverse<true>(V.S, 0, o, d, d4.w, &h) : wide_traverse<true>(V.S, 0, o, d, d4.w, &h);
     if (occluded) return;
-    const float4 c = V.sh_c[slot];
-    float4 r = V.radiance[slot];
-    r.x += c.x; r.y += c.y; r.z += c.z;
-    V.radiance[slot] = r;
+    const float4 c = V.shadow[slot].c;
+    r->x += c.x; r->y += c.y; r->z += c.z;
 }
 
 // ---- probe ---------------------------------------------------------------------------------------------------------------
 // returns 1 when the lights-TLAS probe hit a light and a world shadow ray was traced
-PTB_HD uint32_t probe_slot(const RenderView& V, uint32_t slot)
+template <bool BIN>
+PTB_HD uint32_t probe_contrib_t(const RenderView& V, uint32_t slot, V3 o, float4* r)
 {
-    const float4 o4 = V.nee_o[slot], d4 = V.pr_d[slot];
-    const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
+    const float4 d4 = V.probe[slot].d;
+    const V3 d = ex::v3(d4.x, d4.y, d4.z);
     Hit h;
     h.inst = 0xffffffffu;
-    const bool lit = V.extend_kernel ? bin_traverse<false>(V.S, 1, o, d, ex::inf(), &h) : wide_traverse<false>(V.S, 1, o, d, ex::inf(), &h);  // integrator.rs:100
+    const bool lit = BIN ? bin_traverse<false>(V.S, 1, o, d, ex::inf(), &h) : wide_traverse<false>(V.S, 1, o, d, ex::inf(), &h);  // integrator.rs:100
     if (!lit) return 0u;
     Hit dummy;
     const float tl = h.t;
-    const bool occluded = V.extend_kernel ? bin_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy) : wide_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy);  // :103
+    const bool occluded = BIN ? bin_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy) : wide_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy);  // :103
     if (occluded) return 1u;
-    const uint32_t prim = V.extend_kernel ? h.slot_or_prim : V.S.tri_prim[h.slot_or_prim];
+    const uint32_t prim = BIN ? h.slot_or_prim : V.S.tri_prim[h.slot_or_prim];
     V3 ln;
     bool ff;
     finish_hit(V.S, d, h.inst, prim, h.u, h.v, &ln, &ff);
@@ -368,11 +403,25 @@ PTB_HD uint32_t probe_slot(const RenderView& V, uint32_t slot)
     const float light_pdf = sample_pdf * (tl * tl / cosine);
     const float bp = d4.w;
     const float wgt = (bp * bp) / (bp * bp + light_pdf * light_pdf);  // mis_heuristic<2>(bsdf_pdf, light_pdf)
-    const float4 f = V.pr_f[slot];
-    float4 r = V.radiance[slot];
-    r.x += lmat.colour.x * wgt * f.x; r.y += lmat.colour.y * wgt * f.y; r.z += lmat.colour.z * wgt * f.z;
-    V.radiance[slot] = r;
+    const float4 f = V.probe[slot].f;
+    r->x += lmat.colour.x * wgt * f.x; r->y += lmat.colour.y * wgt * f.y; r->z += lmat.colour.z * wgt * f.z;
     return 1u;
 }
+
+// ---- nee: both direct-light estimates of one bounce (estimate_direct, integrator.rs:138), one read-modify-write of the radiance --------
+// flags: WF_SHADOW | WF_PROBE as returned by shade_slot; returns 1 when the probe traced its world shadow ray
+template <bool BIN>
+PTB_HD uint32_t nee_slot_t(const RenderView& V, uint32_t slot, uint32_t flags)
+{
+    const float4 o4 = V.ray[slot].o;
+    const V3 o = ex::v3(o4.x, o4.y, o4.z);
+    float4 r = V.path[slot].radiance;
+    uint32_t traced = 0u;
+    if (flags & WF_SHADOW) shadow_contrib_t<BIN>(V, slot, o, &r);
+    if (flags & WF_PROBE) traced = probe_contrib_t<BIN>(V, slot, o, &r);
+    V.path[slot].radiance = r;
+    return traced;
+}
+PTB_HD uint32_t nee_slot(const RenderView& V, uint32_t slot, uint32_t flags) { return V.extend_kernel ? nee_slot_t<true>(V, slot, flags) : nee_slot_t<false>(V, slot, flags); }
 
 }  // namespace ptb

@@ -119,16 +119,17 @@ void emu_render(void* h, const float* cam_m16, const float* cam_eye3, uint32_t W
     V.W = W; V.H = H; V.sample_begin = sample_begin; V.sample_count = sample_count; V.seed = seed; V.max_bounces = max_bounces;
     V.enable_nee = enable_nee ? 1u : 0u;
     V.extend_kernel = extend_kernel ? 1u : 0u;
-    std::vector<float4> ray_o(npix), ray_d(npix), weight(npix), radiance(npix), hit_tn(npix), nee_o(npix), sh_d(npix), sh_c(npix), pr_d(npix), pr_f(npix);
-    std::vector<uint2> rng(npix);
+    std::vector<RayRec> ray(npix);
+    std::vector<PathRec> path(npix);
+    std::vector<HitRec> hitrec(npix);
+    std::vector<ShadowRec> shrec(npix);
+    std::vector<ProbeRec> prrec(npix);
     std::vector<unsigned long long> volset(npix);
-    std::vector<uint32_t> hit_info(npix);
     V.accum = (float4*)accum; V.accum_sq = nullptr; V.position = (float4*)position; V.id = id;
-    V.ray_o = ray_o.data(); V.ray_d = ray_d.data(); V.weight = weight.data(); V.radiance = radiance.data(); V.rng = rng.data();
+    V.ray = ray.data(); V.path = path.data(); V.hit = hitrec.data(); V.shadow = shrec.data(); V.probe = prrec.data();
     V.volset = sc.volumes.empty() ? nullptr : volset.data();
-    V.hit_tn = hit_tn.data(); V.hit_info = hit_info.data(); V.nee_o = nee_o.data(); V.sh_d = sh_d.data(); V.sh_c = sh_c.data(); V.pr_d = pr_d.data(); V.pr_f = pr_f.data();
-    std::vector<uint32_t> ext, next, term, shadow, probe;
-    for (uint32_t i = 0; i < npix; ++i) { ray_o[i].w = 0.0f; ray_d[i].w = 0.0f; term.push_back(i); }
+    std::vector<uint32_t> ext, next, term, nee;
+    for (uint32_t i = 0; i < npix; ++i) { ray[i].o.w = 0.0f; ray[i].d.w = 0.0f; term.push_back(i); }
     uint64_t n_extend = 0, n_shadow = 0, n_probe = 0, n_paths = 0, n_iters = 0;
     for (;;)
     {
@@ -146,17 +147,18 @@ void emu_render(void* h, const float* cam_m16, const float* cam_eye3, uint32_t W
             for (uint32_t s : mat[k])
             {
                 const uint32_t f = shade_slot(V, s);
-                if (f & WF_SHADOW) shadow.push_back(s);
-                if (f & WF_PROBE) probe.push_back(s);
+                if (f & (WF_SHADOW | WF_PROBE)) nee.push_back(s | ((f & WF_SHADOW) ? NEE_SHADOW_BIT : 0u) | ((f & WF_PROBE) ? NEE_PROBE_BIT : 0u));
                 if (f & WF_NEXT) next.push_back(s);
                 if (f & WF_TERM) term.push_back(s);
             }
-        for (uint32_t s : shadow) shadow_slot(V, s);
-        n_shadow += shadow.size();
-        for (uint32_t s : probe) n_shadow += probe_slot(V, s);
-        n_probe += probe.size();
-        shadow.clear();
-        probe.clear();
+        for (uint32_t e : nee)
+        {
+            const uint32_t f = ((e & NEE_SHADOW_BIT) ? WF_SHADOW : 0u) | ((e & NEE_PROBE_BIT) ? WF_PROBE : 0u);
+            n_shadow += (f & WF_SHADOW) ? 1 : 0;
+            n_probe += (f & WF_PROBE) ? 1 : 0;
+            n_shadow += nee_slot(V, e & NEE_SLOT_MASK, f);
+        }
+        nee.clear();
     }
     if (counters) { counters[0] += n_extend; counters[1] += n_shadow; counters[2] += n_probe; counters[3] += n_paths; counters[4] += n_iters; }
 }

@@ -21,6 +21,8 @@ t0 = time.time(); ctx.render(0, spp, seed=1, max_bounces=sd.max_bounces); ctx.sy
 c = ctx.counters(); t = ctx.timing()
 rays = c["extend"] + c["shadow"]
 ms = t["render"][0]
+log = ctx.iteration_log()
+print("iterations", len(log), "active@", {int(i): int(log[i]) for i in sorted(set([0, 1, 2, 4, 8, 16, 32, 64, 128, 256, 512, len(log) - 1])) if i < len(log)})
 print(json.dumps(dict(scene=sd.name, W=W, H=H, spp=spp, build_s=round(t_build, 2), stats=ctx.bvh_stats(), counters=c, render_ms=ms, wall_ms=wall * 1e3,
                       mrays_s=rays / ms / 1e3, timing={k: (round(v[0], 2), v[1]) for k, v in t.items()}, opts=opts)))
 # trace-only probes
