@@ -80,6 +80,9 @@ struct ptb_context
     int opt_extend_kernel = 0;  // 0 wide, 1 reference-order
     int opt_block_threads = 128;
     int opt_blocks_per_sm = 8;
+    int opt_refill_below = 16;    // persistent kernels refill idle lanes when fewer than this many lanes of a warp are traversing
+    int opt_node_quorum = 8;      // lanes of a warp that must want the node stage before it runs (1 = never postponed)
+    int opt_extend_blocks = 6, opt_nee_blocks = 5;  // resident blocks per SM (launch bounds -> register cap) of k_extend / k_nee
     int opt_tail_threshold = -1;  // active slots at which ptb_render switches to the tail kernel (<0 automatic, 0 never)
     int profiling = 0;
     int second_moment = 0;
@@ -125,5 +128,5 @@ struct TraceArgs
     float* normal;
     unsigned long long* counter;
 };
-cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream);
+cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream, int refill_below, int node_quorum);
 }  // namespace ptb

@@ -27,6 +27,12 @@ PTB_HD float sub(float a, float b) { return __fsub_rn(a, b); }
 PTB_HD float div(float a, float b) { return __fdiv_rn(a, b); }
 PTB_HD float fma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
 PTB_HD float sqrt(float a) { return __fsqrt_rn(a); }
+PTB_HD float rcp(float a) { return __frcp_rn(a); }  // correctly rounded 1/a == __fdiv_rn(1, a), without the general division
+// min/max for the slab test: one FMNMX each.  They differ from SSE minps/maxps only when the SECOND operand is NaN or for
+// the sign of a zero result; in AABB::intersect_t the second operand is EPSILON, t_max or a value already clamped by one
+// of them (never NaN), and a zero's sign cannot change the comparison or the returned t >= EPSILON.
+PTB_HD float mn_fast(float a, float b) { return fminf(a, b); }
+PTB_HD float mx_fast(float a, float b) { return fmaxf(a, b); }
 PTB_HD uint32_t bits(float f) { return __float_as_uint(f); }
 PTB_HD float from_bits(uint32_t u) { return __uint_as_float(u); }
 #else
@@ -36,6 +42,9 @@ PTB_HD float sub(float a, float b) { return a - b; }
 PTB_HD float div(float a, float b) { return a / b; }
 PTB_HD float fma(float a, float b, float c) { return std::fmaf(a, b, c); }
 PTB_HD float sqrt(float a) { return std::sqrt(a); }
+PTB_HD float rcp(float a) { return 1.0f / a; }
+PTB_HD float mn_fast(float a, float b) { return (a < b) ? a : b; }
+PTB_HD float mx_fast(float a, float b) { return (a > b) ? a : b; }
 PTB_HD uint32_t bits(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
 PTB_HD float from_bits(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
 #endif
@@ -81,7 +90,7 @@ PTB_HD V3 cross(V3 a, V3 b)
 }
 PTB_HD float length(V3 a) { return sqrt(dot3(a, a)); }
 PTB_HD V3 normalize(V3 a) { return div(a, sqrt(dot3(a, a))); }
-PTB_HD V3 recip(V3 a) { return v3(div(1.0f, a.x), div(1.0f, a.y), div(1.0f, a.z)); }
+PTB_HD V3 recip(V3 a) { return v3(rcp(a.x), rcp(a.y), rcp(a.z)); }
 // Mat3A * Vec3A = ((c0*x + c1*y) + c2*z)
 PTB_HD V3 m3_mul(V3 c0, V3 c1, V3 c2, V3 v) { return add(add(mul(c0, v.x), mul(c1, v.y)), mul(c2, v.z)); }
 // Ray::at (ray.rs:20): direction.mul_add(splat(t), origin), fused
@@ -96,12 +105,11 @@ PTB_HD bool slab(V3 lo, V3 hi, V3 o, V3 inv, float t_max, float* t_enter)
 {
     V3 t0 = mul(sub(lo, o), inv);
     V3 t1 = mul(sub(hi, o), inv);
-    V3 e = v3(EPS, EPS, EPS), m = v3(t_max, t_max, t_max);
-    V3 ts = vmin(vmax(t0, e), vmax(t1, e));
-    V3 tb = vmax(vmin(t0, m), vmin(t1, m));
-    float t = mx(mx(ts.x, ts.y), ts.z);
+    float lx = mn_fast(mx_fast(t0.x, EPS), mx_fast(t1.x, EPS)), ly = mn_fast(mx_fast(t0.y, EPS), mx_fast(t1.y, EPS)), lz = mn_fast(mx_fast(t0.z, EPS), mx_fast(t1.z, EPS));
+    float hx = mx_fast(mn_fast(t0.x, t_max), mn_fast(t1.x, t_max)), hy = mx_fast(mn_fast(t0.y, t_max), mn_fast(t1.y, t_max)), hz = mx_fast(mn_fast(t0.z, t_max), mn_fast(t1.z, t_max));
+    float t = mx_fast(mx_fast(lx, ly), lz);
     *t_enter = t;
-    return t <= mn(mn(tb.x, tb.y), tb.z);
+    return t <= mn_fast(mn_fast(hx, hy), hz);
 }
 PTB_HD float surface_area(V3 lo, V3 hi)  // boundingbox.rs:90-95
 {

@@ -2,12 +2,69 @@
 // Persistent threads: the grid is a multiple of the SM count and every warp pulls batches of 32 rays from a global
 // counter until the batch is exhausted (one atomic per warp-batch).  The per-ray work is traverse.h.
 #include "context.h"
-#include "traverse.h"
+#include "persist.cuh"
 
 namespace ptb {
 
-template <bool WIDE, bool ANY>
-__global__ void __launch_bounds__(128) trace_kernel(SceneDev S, int which, unsigned long long n, TraceArgs a)
+__device__ __forceinline__ void write_result(const SceneDev& S, int which, const TraceArgs& a, unsigned long long i, bool any, bool f, const Hit& h, uint32_t prim_raw_is_slot, V3 d)
+{
+    a.hit[i] = f ? 1 : 0;
+    if (any) return;
+    uint32_t prim = 0xffffffffu, blas = 0xffffffffu, inst = 0xffffffffu;
+    V3 nn = ex::v3(0.0f, 0.0f, 0.0f);
+    bool ff = false;
+    if (f)
+    {
+        prim = prim_raw_is_slot ? S.tri_prim[h.slot_or_prim] : h.slot_or_prim;
+        blas = S.inst[h.inst].blas;
+        inst = h.inst - S.tlas[which].inst_base;
+        finish_hit(S, d, h.inst, prim, h.u, h.v, &nn, &ff);
+    }
+    if (a.t) a.t[i] = f ? h.t : ex::inf();
+    if (a.u) a.u[i] = f ? h.u : 0.0f;
+    if (a.v) a.v[i] = f ? h.v : 0.0f;
+    if (a.prim) a.prim[i] = prim;
+    if (a.blas) a.blas[i] = blas;
+    if (a.inst) a.inst[i] = inst;
+    if (a.front) a.front[i] = ff ? 1 : 0;
+    if (a.normal) { a.normal[i * 3] = nn.x; a.normal[i * 3 + 1] = nn.y; a.normal[i * 3 + 2] = nn.z; }
+}
+
+// 8-wide layout: dynamic-fetch persistent kernel (persist.cuh)
+template <bool ANY>
+struct TraceJob
+{
+    const SceneDev& S;
+    const TraceArgs& a;
+    int which;
+    unsigned long long base;
+    unsigned long long i = 0;
+    __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
+    {
+        i = base + idx;
+        wide_begin(tr, S, which, ex::v3(a.o[i * 3], a.o[i * 3 + 1], a.o[i * 3 + 2]), ex::v3(a.d[i * 3], a.d[i * 3 + 1], a.d[i * 3 + 2]), a.tmax[i], ANY);
+        return true;
+    }
+    __device__ __forceinline__ bool finish(WideTrav& tr, bool mine)
+    {
+        if (!mine) return false;
+        Hit h;
+        h.t = tr.t_max; h.u = tr.hit_u; h.v = tr.hit_v; h.slot_or_prim = tr.hit_slot; h.inst = tr.hit_inst;
+        write_result(S, which, a, i, ANY, tr.hit_inst != TRAV_NONE, h, 1u, tr.dw);
+        return false;
+    }
+};
+
+template <bool ANY>
+__global__ void __launch_bounds__(128) trace_wide_kernel(SceneDev S, int which, unsigned long long base, uint32_t n, TraceArgs a, int refill_below, int node_quorum)
+{
+    TraceJob<ANY> job{S, a, which, base};
+    persistent_trace<ANY ? 1 : 0>(S, job, (uint32_t*)a.counter, n, refill_below, node_quorum);
+}
+
+// reference-order binary kernel: every warp pulls batches of 32 rays from a global counter, one ray per lane
+template <bool ANY>
+__global__ void __launch_bounds__(128) trace_bin_kernel(SceneDev S, int which, unsigned long long n, TraceArgs a)
 {
     const unsigned lane = threadIdx.x & 31u;
     for (;;)
@@ -22,44 +79,32 @@ __global__ void __launch_bounds__(128) trace_kernel(SceneDev S, int which, unsig
         const V3 d = ex::v3(a.d[i * 3], a.d[i * 3 + 1], a.d[i * 3 + 2]);
         Hit h;
         h.inst = 0xffffffffu;
-        const bool f = WIDE ? wide_traverse<ANY>(S, which, o, d, a.tmax[i], &h) : bin_traverse<ANY>(S, which, o, d, a.tmax[i], &h);
-        a.hit[i] = f ? 1 : 0;
-        if (ANY) continue;
-        uint32_t prim = 0xffffffffu, blas = 0xffffffffu, inst = 0xffffffffu;
-        V3 nn = ex::v3(0.0f, 0.0f, 0.0f);
-        bool ff = false;
-        if (f)
-        {
-            prim = WIDE ? S.tri_prim[h.slot_or_prim] : h.slot_or_prim;
-            blas = S.inst[h.inst].blas;
-            inst = h.inst - S.tlas[which].inst_base;
-            finish_hit(S, d, h.inst, prim, h.u, h.v, &nn, &ff);
-        }
-        if (a.t) a.t[i] = f ? h.t : ex::inf();
-        if (a.u) a.u[i] = f ? h.u : 0.0f;
-        if (a.v) a.v[i] = f ? h.v : 0.0f;
-        if (a.prim) a.prim[i] = prim;
-        if (a.blas) a.blas[i] = blas;
-        if (a.inst) a.inst[i] = inst;
-        if (a.front) a.front[i] = ff ? 1 : 0;
-        if (a.normal) { a.normal[i * 3] = nn.x; a.normal[i * 3 + 1] = nn.y; a.normal[i * 3 + 2] = nn.z; }
+        const bool f = bin_traverse<ANY>(S, which, o, d, a.tmax[i], &h);
+        write_result(S, which, a, i, ANY, f, h, 0u, d);
     }
 }
 
-cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream)
+cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream, int refill_below, int node_quorum)
 {
-    cudaError_t e = cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), stream);
-    if (e != cudaSuccess) return e;
     const int blocks = sm_count * 8;
     if (kernel == 0)
     {
-        if (any_hit) trace_kernel<true, true><<<blocks, 128, 0, stream>>>(S, which, n, a);
-        else trace_kernel<true, false><<<blocks, 128, 0, stream>>>(S, which, n, a);
+        // the persistent loop indexes work items with 32 bits: split larger batches
+        for (uint64_t base = 0; base < n; base += 0x40000000ull)
+        {
+            cudaError_t e = cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), stream);
+            if (e != cudaSuccess) return e;
+            const uint32_t cnt = (uint32_t)std::min<uint64_t>(n - base, 0x40000000ull);
+            if (any_hit) trace_wide_kernel<true><<<blocks, 128, 0, stream>>>(S, which, base, cnt, a, refill_below, node_quorum);
+            else trace_wide_kernel<false><<<blocks, 128, 0, stream>>>(S, which, base, cnt, a, refill_below, node_quorum);
+        }
     }
     else
     {
-        if (any_hit) trace_kernel<false, true><<<blocks, 128, 0, stream>>>(S, which, n, a);
-        else trace_kernel<false, false><<<blocks, 128, 0, stream>>>(S, which, n, a);
+        cudaError_t e = cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), stream);
+        if (e != cudaSuccess) return e;
+        if (any_hit) trace_bin_kernel<true><<<blocks, 128, 0, stream>>>(S, which, n, a);
+        else trace_bin_kernel<false><<<blocks, 128, 0, stream>>>(S, which, n, a);
     }
     return cudaGetLastError();
 }

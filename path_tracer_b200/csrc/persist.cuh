@@ -1,0 +1,89 @@
+// persist.cuh — persistent-thread ray loop with dynamic fetch (device only).
+//
+// Every warp keeps 32 rays in flight: a lane whose traversal has finished hands its result to the job (`finish`, executed
+// convergently so the job can use warp-aggregated queue pushes), and as soon as fewer than `refill_below` lanes are still
+// traversing the idle lanes fetch new work items with one atomicAdd for the whole warp.  Between refills all busy lanes run
+// wide_step() (traverse.h), whose stages sit at single code locations, so the lanes of a warp re-converge at every step
+// whatever mix of TLAS nodes, BLAS nodes, leaves and triangles they are at.
+//
+// Job interface (per lane):
+//   bool start(uint32_t index, WideTrav& tr)   fetch work item `index`, call wide_begin; false = the item needs no traversal
+//   bool finish(WideTrav& tr, bool mine)       called by ALL lanes of the warp together; `mine` = this lane's traversal just
+//                                              ended.  May begin a follow-up traversal for the lane (return true).
+#pragma once
+#include "traverse.h"
+
+namespace ptb {
+
+template <int MODE, class Job>
+__device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, uint32_t* cursor, uint32_t total, int refill_below, int node_quorum)
+{
+    uint2 stack[WIDE_STACK_CAP];
+    WideTrav tr;
+    const unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u;
+    int state = 0;  // 0 idle, 1 traversing, 2 traversal finished (result not yet consumed)
+    // Work distribution: the warp takes BATCH consecutive items from the global cursor at a time (one atomicAdd per BATCH
+    // items, not per refill) and deals them out to its idle lanes from the warp-uniform range [wbase, wend).
+    // Near the end of the queue the batch shrinks to what the idle lanes need right now, so that no warp is left holding a
+    // long private backlog while the others have run dry.
+    constexpr uint32_t BATCH = 64;
+    const uint32_t fine_below = (gridDim.x * blockDim.x >> 5) * (2u * BATCH);
+    uint32_t wbase = 0, wend = 0, seen = 0;
+    bool global_more = total > 0u;
+    for (;;)
+    {
+        if (__any_sync(FULL, state == 2))
+        {
+            const bool again = job.finish(tr, state == 2);
+            if (state == 2) state = again ? 1 : 0;
+        }
+        if (wbase < wend || global_more)
+        {
+            const unsigned idle = __ballot_sync(FULL, state == 0);
+            if (idle)
+            {
+                if (wbase >= wend)
+                {
+                    const uint32_t want = (total - seen > fine_below) ? BATCH : (uint32_t)__popc(idle);
+                    uint32_t base = 0;
+                    if (lane == 0u) base = atomicAdd(cursor, want);
+                    base = __shfl_sync(FULL, base, 0);
+                    if (base >= total) { global_more = false; wbase = wend = 0u; }
+                    else { wbase = base; wend = min(base + want, total); seen = wend; if (wend == total) global_more = false; }
+                }
+                const uint32_t avail = wend - wbase, n = (uint32_t)__popc(idle);
+                const uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
+                if (state == 0 && rank < avail && job.start(wbase + rank, tr)) state = 1;
+                wbase += min(n, avail);
+            }
+        }
+        const bool more = wbase < wend || global_more;
+        unsigned busy = __ballot_sync(FULL, state == 1);
+        if (!busy)
+        {
+            if (!more && !__any_sync(FULL, state == 2)) break;
+            continue;
+        }
+        const int keep = more ? refill_below : 1;
+        do
+        {
+            if (state == 1 && !wide_step_pop(tr, S, stack)) state = 2;
+            // the node stage runs when at least node_quorum lanes want it, or when no lane has leaf/triangle work left
+            const unsigned wn = __ballot_sync(FULL, state == 1 && wide_wants_node(tr));
+            const unsigned wl = __ballot_sync(FULL, state == 1 && wide_has_leaf_work(tr));
+            const bool allow = __popc(wn) >= node_quorum || wl == 0u;
+            if (state == 1 && !wide_step_work<MODE>(tr, S, stack, allow)) state = 2;
+            busy = __ballot_sync(FULL, state == 1);
+        } while (__popc(busy) >= keep);
+    }
+}
+
+__device__ __forceinline__ unsigned long long warp_sum(unsigned long long v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+}  // namespace ptb

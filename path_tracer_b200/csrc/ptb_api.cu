@@ -351,7 +351,7 @@ int ptb_trace_resident(ptb_context* ctx, int which, int kernel, int any_hit, int
     PTB_CUDA(ctx, cudaEventCreate(&e1));
     TraceArgs a = trace_args(ctx);
     PTB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
-    for (int r = 0; r < repeats; ++r) PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, any_hit, ctx->t_n, a, ctx->sm_count, ctx->stream));
+    for (int r = 0; r < repeats; ++r) PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, any_hit, ctx->t_n, a, ctx->sm_count, ctx->stream, ctx->opt_refill_below, ctx->opt_node_quorum));
     PTB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
     PTB_CUDA(ctx, cudaEventSynchronize(e1));
     float ms = 0;
@@ -386,7 +386,7 @@ int ptb_trace_closest(ptb_context* ctx, int which, int kernel, uint64_t n, const
     if (n == 0) return PTB_OK;  // empty batch
     int rc = ptb_trace_upload(ctx, n, o3, d3, tmax);
     if (rc != PTB_OK) return rc;
-    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 0, n, trace_args(ctx), ctx->sm_count, ctx->stream));
+    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 0, n, trace_args(ctx), ctx->sm_count, ctx->stream, ctx->opt_refill_below, ctx->opt_node_quorum));
 #define DL(dst, src, bytes) \
     if (dst) PTB_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream))
     DL(hit, ctx->t_hit.p, n);
@@ -412,7 +412,7 @@ int ptb_trace_any(ptb_context* ctx, int which, int kernel, uint64_t n, const flo
     if (n == 0) return PTB_OK;
     int rc = ptb_trace_upload(ctx, n, o3, d3, tmax);
     if (rc != PTB_OK) return rc;
-    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 1, n, trace_args(ctx), ctx->sm_count, ctx->stream));
+    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 1, n, trace_args(ctx), ctx->sm_count, ctx->stream, ctx->opt_refill_below, ctx->opt_node_quorum));
     PTB_CUDA(ctx, cudaMemcpyAsync(hit, ctx->t_hit.p, n, cudaMemcpyDeviceToHost, ctx->stream));
     PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return PTB_OK;
@@ -427,7 +427,11 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "extend_kernel") ctx->opt_extend_kernel = value;
     else if (n == "block_threads") ctx->opt_block_threads = value;
     else if (n == "blocks_per_sm") ctx->opt_blocks_per_sm = value;
+    else if (n == "node_quorum") ctx->opt_node_quorum = value;
+    else if (n == "extend_blocks") ctx->opt_extend_blocks = value;
+    else if (n == "nee_blocks") ctx->opt_nee_blocks = value;
     else if (n == "tail_threshold") ctx->opt_tail_threshold = value;
+    else if (n == "refill_below") ctx->opt_refill_below = value < 1 ? 1 : (value > 32 ? 32 : value);
     else return ctx->fail(PTB_ERR_INVALID, "unknown option " + n);
     return PTB_OK;
 }

@@ -20,6 +20,7 @@
 
 #include "camera_host.h"
 #include "context.h"
+#include "persist.cuh"
 #include "wavefront.h"
 
 namespace ptb {
@@ -121,51 +122,118 @@ __global__ void __launch_bounds__(128) k_init(RenderView V, Queues Q)
     }
 }
 
-template <bool SORT, bool BIN>
-__global__ void __launch_bounds__(128) k_extend(RenderView V, Queues Q, uint32_t it)
+// ---- extend: dynamic-fetch persistent kernel over the 8-wide layout --------------------------------------------------------
+struct ExtendJob
+{
+    const RenderView& V;
+    const Queues& Q;
+    WfSet& S;
+    uint32_t b, n_cont, n_term;
+    bool sort;
+    uint32_t slot = 0;
+    unsigned long long paths = 0;
+
+    __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
+    {
+        V3 o, d;
+        if (idx < n_cont)
+        {
+            slot = Q.cont[b][idx];
+            const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
+            o = ex::v3(o4.x, o4.y, o4.z);
+            d = ex::v3(d4.x, d4.y, d4.z);
+        }
+        else
+        {
+            slot = Q.term[b][idx - n_cont];
+            if (!(regen_slot(V, slot, &o, &d) & WF_NEXT)) return false;
+            ++paths;
+        }
+        wide_begin(tr, V.S, 0, o, d, ex::inf(), false);
+        return true;
+    }
+    __device__ __forceinline__ bool finish(WideTrav& tr, bool mine)
+    {
+        uint32_t kind = 0xffu;
+        if (mine)
+        {
+            if (tr.hit_inst == TRAV_NONE)
+            {
+                V.hit[slot].info = 0xffffffffu;
+                kind = Q_MISS;
+            }
+            else
+            {
+                const uint32_t prim = V.S.tri_prim[tr.hit_slot];
+                V3 n;
+                bool ff;
+                finish_hit(V.S, tr.dw, tr.hit_inst, prim, tr.hit_u, tr.hit_v, &n, &ff);
+                V.hit[slot].tn = f4(tr.t_max, n.x, n.y, n.z);
+                V.hit[slot].info = tr.hit_inst | (ff ? 0x80000000u : 0u);
+                kind = V.S.mat[V.S.inst[tr.hit_inst].blas].kind;
+            }
+            if (!sort) kind = 0u;
+        }
+        warp_push_keyed(Q.mat, Q.npix, S.n_mat, kind, slot);
+        return false;
+    }
+};
+
+template <int MB>
+__global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint32_t it, int sort, int refill_below, int node_quorum)
 {
     WfSet& S = Q.c->set[it % 3u];
-    const uint32_t b = it & 1u;
     const uint32_t n_cont = S.n_cont, n_term = S.n_term;
     if (blockIdx.x == 0 && threadIdx.x == 0)
     {
         Q.c->set[(it + 2u) % 3u] = WfSet{};  // consumed in iteration it-1, refilled from iteration it+1 on
         if (n_cont + n_term) Q.c->stat_iters += 1;
     }
-    const uint32_t nc_c = (n_cont + 31u) >> 5, nc_t = (n_term + 31u) >> 5;
+    ExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort != 0};
+    persistent_trace<0>(V.S, job, &S.cur_extend, n_cont + n_term, refill_below, node_quorum);
+    const unsigned long long p = warp_sum(job.paths);
+    if ((threadIdx.x & 31u) == 0u && p) atomicAdd(&Q.c->stat_paths, p);
+}
+
+// reference-order variant (binary trees, reference visit order): static chunks of 32, one ray per lane
+__global__ void __launch_bounds__(128) k_extend_bin(RenderView V, Queues Q, uint32_t it)
+{
+    WfSet& S = Q.c->set[it % 3u];
+    const uint32_t b = it & 1u;
+    const uint32_t n_cont = S.n_cont, n_term = S.n_term;
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+    {
+        Q.c->set[(it + 2u) % 3u] = WfSet{};
+        if (n_cont + n_term) Q.c->stat_iters += 1;
+    }
+    const uint32_t total = n_cont + n_term;
     const uint32_t lane = threadIdx.x & 31u;
     uint32_t c;
-    while (fetch_chunk(&S.cur_extend, nc_c + nc_t, &c))
+    while (fetch_chunk(&S.cur_extend, (total + 31u) >> 5, &c))
     {
+        const uint32_t i = c * 32u + lane;
         uint32_t slot = 0;
-        bool valid;
+        bool valid = i < total;
         V3 o = ex::v3(0, 0, 0), d = ex::v3(0, 0, 1);
-        if (c < nc_c)
+        bool fresh = false;
+        if (valid)
         {
-            const uint32_t i = c * 32u + lane;
-            valid = i < n_cont;
-            if (valid)
+            if (i < n_cont)
             {
                 slot = Q.cont[b][i];
                 const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
                 o = ex::v3(o4.x, o4.y, o4.z);
                 d = ex::v3(d4.x, d4.y, d4.z);
             }
-        }
-        else
-        {
-            const uint32_t i = (c - nc_c) * 32u + lane;
-            valid = i < n_term;
-            if (valid)
+            else
             {
-                slot = Q.term[b][i];
-                valid = (regen_slot(V, slot, &o, &d) & WF_NEXT) != 0u;
+                slot = Q.term[b][i - n_cont];
+                valid = fresh = (regen_slot(V, slot, &o, &d) & WF_NEXT) != 0u;
             }
-            const unsigned m = __ballot_sync(0xffffffffu, valid);
-            if (lane == 0u && m) atomicAdd(&Q.c->stat_paths, (unsigned long long)__popc(m));
         }
-        uint32_t kind = valid ? extend_ray_t<BIN>(V, slot, o, d) : 0xffu;
-        if (!SORT && valid) kind = 0u;
+        const unsigned m = __ballot_sync(0xffffffffu, fresh);
+        if (lane == 0u && m) atomicAdd(&Q.c->stat_paths, (unsigned long long)__popc(m));
+        const uint32_t kind = valid ? extend_ray_t<true>(V, slot, o, d) : 0xffu;
         warp_push_keyed(Q.mat, Q.npix, S.n_mat, kind, slot);
     }
 }
@@ -200,8 +268,97 @@ __global__ void __launch_bounds__(128) k_shade(RenderView V, Queues Q, uint32_t 
     }
 }
 
-template <bool BIN>
-__global__ void __launch_bounds__(128) k_nee(RenderView V, Queues Q, uint32_t it)
+// ---- nee: both direct-light estimates of a bounce as a chain of up to three traversals per lane -----------------------------------
+//   stage 0  world any-hit towards the explicit light sample            (integrator.rs:56)
+//   stage 1  lights-TLAS closest hit along the BSDF-sampled direction    (integrator.rs:100)
+//   stage 2  world any-hit up to that light                              (integrator.rs:103)
+struct NeeJob
+{
+    const RenderView& V;
+    const Queues& Q;
+    uint32_t slot = 0, flags = 0, stage = 0;
+    V3 o;
+    float4 r;
+    // light hit of stage 1
+    float lt = 0, lu = 0, lv = 0;
+    uint32_t lslot = 0, linst = 0;
+    unsigned long long n_shadow = 0, n_probe = 0, n_probe_shadow = 0;
+
+    __device__ __forceinline__ void begin_probe(WideTrav& tr)
+    {
+        const float4 d4 = V.probe[slot].d;
+        wide_begin(tr, V.S, 1, o, ex::v3(d4.x, d4.y, d4.z), ex::inf(), false);
+        stage = 1;
+        ++n_probe;
+    }
+    __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
+    {
+        const uint32_t e = Q.nee[idx];
+        slot = e & NEE_SLOT_MASK;
+        flags = ((e & NEE_SHADOW_BIT) ? WF_SHADOW : 0u) | ((e & NEE_PROBE_BIT) ? WF_PROBE : 0u);
+        const float4 o4 = V.ray[slot].o;
+        o = ex::v3(o4.x, o4.y, o4.z);
+        r = V.path[slot].radiance;
+        if (flags & WF_SHADOW)
+        {
+            const float4 d4 = V.shadow[slot].d;
+            wide_begin(tr, V.S, 0, o, ex::v3(d4.x, d4.y, d4.z), d4.w, true);
+            stage = 0;
+            ++n_shadow;
+        }
+        else begin_probe(tr);
+        return true;
+    }
+    __device__ __forceinline__ bool finish(WideTrav& tr, bool mine)
+    {
+        if (!mine) return false;
+        if (stage == 0)
+        {
+            if (tr.hit_inst == TRAV_NONE)
+            {
+                const float4 c = V.shadow[slot].c;
+                r.x += c.x; r.y += c.y; r.z += c.z;
+            }
+            if (flags & WF_PROBE) { begin_probe(tr); return true; }
+        }
+        else if (stage == 1)
+        {
+            if (tr.hit_inst != TRAV_NONE)
+            {
+                lt = tr.t_max; lu = tr.hit_u; lv = tr.hit_v; lslot = tr.hit_slot; linst = tr.hit_inst;
+                wide_begin(tr, V.S, 0, o, tr.dw, lt * (1.0f - ex::EPS), true);
+                stage = 2;
+                ++n_probe_shadow;
+                return true;
+            }
+        }
+        else if (tr.hit_inst == TRAV_NONE)
+        {
+            const V3 c = probe_light_contrib(V, slot, tr.dw, lt, lu, lv, V.S.tri_prim[lslot], linst);
+            r.x += c.x; r.y += c.y; r.z += c.z;
+        }
+        V.path[slot].radiance = r;
+        return false;
+    }
+};
+
+template <int MB>
+__global__ void __launch_bounds__(128, MB) k_nee(RenderView V, Queues Q, uint32_t it, int refill_below, int node_quorum)
+{
+    WfSet& S = Q.c->set[it % 3u];
+    NeeJob job{V, Q};
+    persistent_trace<2>(V.S, job, &S.cur_nee, S.n_nee, refill_below, node_quorum);
+    const unsigned long long a = warp_sum(job.n_shadow), b = warp_sum(job.n_probe), c = warp_sum(job.n_probe_shadow);
+    if ((threadIdx.x & 31u) == 0u)
+    {
+        if (a) atomicAdd(&Q.c->stat_shadow, a);
+        if (b) atomicAdd(&Q.c->stat_probe, b);
+        if (c) atomicAdd(&Q.c->stat_probe_shadow, c);
+    }
+}
+
+// reference-order variant: static chunks, one entry per lane
+__global__ void __launch_bounds__(128) k_nee_bin(RenderView V, Queues Q, uint32_t it)
 {
     WfSet& S = Q.c->set[it % 3u];
     const uint32_t n = S.n_nee;
@@ -212,7 +369,7 @@ __global__ void __launch_bounds__(128) k_nee(RenderView V, Queues Q, uint32_t it
         const uint32_t i = c * 32u + lane;
         const uint32_t e = i < n ? Q.nee[i] : 0u;
         const uint32_t flags = ((e & NEE_SHADOW_BIT) ? WF_SHADOW : 0u) | ((e & NEE_PROBE_BIT) ? WF_PROBE : 0u);
-        const uint32_t traced = flags ? nee_slot_t<BIN>(V, e & NEE_SLOT_MASK, flags) : 0u;
+        const uint32_t traced = flags ? nee_slot_t<true>(V, e & NEE_SLOT_MASK, flags) : 0u;
         const unsigned ms = __ballot_sync(0xffffffffu, (flags & WF_SHADOW) != 0u), mp = __ballot_sync(0xffffffffu, (flags & WF_PROBE) != 0u), mt = __ballot_sync(0xffffffffu, traced != 0u);
         if (lane == 0u)
         {
@@ -533,17 +690,37 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     rs.log_iters = 0;
     for (uint32_t it = 0;; ++it)
     {
-        if (bin) k_extend<true, true><<<grid, threads, 0, st>>>(V, Q, it);
-        else if (sort) k_extend<true, false><<<grid, threads, 0, st>>>(V, Q, it);
-        else k_extend<false, false><<<grid, threads, 0, st>>>(V, Q, it);
+        if (bin) k_extend_bin<<<grid, threads, 0, st>>>(V, Q, it);
+        else
+        {
+            const int g = ctx->sm_count * ctx->opt_extend_blocks, so = sort ? 1 : 0, rb = ctx->opt_refill_below;
+            switch (ctx->opt_extend_blocks)
+            {
+            case 5: k_extend<5><<<g, threads, 0, st>>>(V, Q, it, so, rb, ctx->opt_node_quorum); break;
+            case 7: k_extend<7><<<g, threads, 0, st>>>(V, Q, it, so, rb, ctx->opt_node_quorum); break;
+            case 8: k_extend<8><<<g, threads, 0, st>>>(V, Q, it, so, rb, ctx->opt_node_quorum); break;
+            default: k_extend<6><<<ctx->sm_count * 6, threads, 0, st>>>(V, Q, it, so, rb, ctx->opt_node_quorum); break;
+            }
+        }
         PTB_CUDA(ctx, mark(2));
         k_shade<<<grid, threads, 0, st>>>(V, Q, it);
         PTB_CUDA(ctx, mark(3));
         rs.launches += 2;
         if (V.enable_nee)
         {
-            if (bin) k_nee<true><<<grid, threads, 0, st>>>(V, Q, it);
-            else k_nee<false><<<grid, threads, 0, st>>>(V, Q, it);
+            if (bin) k_nee_bin<<<grid, threads, 0, st>>>(V, Q, it);
+            else
+            {
+                const int g = ctx->sm_count * ctx->opt_nee_blocks, rb = ctx->opt_refill_below;
+                switch (ctx->opt_nee_blocks)
+                {
+                case 5: k_nee<5><<<g, threads, 0, st>>>(V, Q, it, rb, ctx->opt_node_quorum); break;
+                case 7: k_nee<7><<<g, threads, 0, st>>>(V, Q, it, rb, ctx->opt_node_quorum); break;
+                case 8: k_nee<8><<<g, threads, 0, st>>>(V, Q, it, rb, ctx->opt_node_quorum); break;
+                case 6: k_nee<6><<<g, threads, 0, st>>>(V, Q, it, rb, ctx->opt_node_quorum); break;
+                default: k_nee<5><<<ctx->sm_count * 5, threads, 0, st>>>(V, Q, it, rb, ctx->opt_node_quorum); break;
+                }
+            }
             PTB_CUDA(ctx, mark(4));
             rs.launches += 1;
         }

@@ -47,18 +47,19 @@ struct TravRay
     uint32_t oi; // 7 ^ octant
 };
 
-PTB_HD float finite_recip(float d)
+// Finite stand-in for 1/d in the conservative quantised tests: 1/d clamped to +-2^60 (|d| < 2^-60, including +-0 whose
+// exact reciprocal is +-inf, is treated as +-2^-60).  Derived from the exact reciprocal, so it costs no second division.
+PTB_HD float finite_recip_of(float inv)
 {
-    const float tiny = 8.6736174e-19f;  // 2^-60
-    float a = fabsf(d) < tiny ? copysignf(tiny, d) : d;
-    return 1.0f / a;
+    const float big = 1.152921504606846976e18f;  // 2^60
+    return fabsf(inv) > big ? copysignf(big, inv) : inv;
 }
 PTB_HD void set_ray(TravRay& r, V3 o, V3 d)
 {
     r.o = o;
     r.d = d;
     r.inv = ex::recip(d);
-    r.idq = ex::v3(finite_recip(d.x), finite_recip(d.y), finite_recip(d.z));
+    r.idq = ex::v3(finite_recip_of(r.inv.x), finite_recip_of(r.inv.y), finite_recip_of(r.inv.z));
     uint32_t oct = (d.x < 0.0f ? 4u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 1u : 0u);
     r.oi = 7u ^ oct;
 }
@@ -70,7 +71,16 @@ PTB_HD void transform_ray(TravRay& out, V3 o, V3 d, const float* inv12)
     set_ray(out, ex::add(ex::m3_mul(c0, c1, c2, o), t), ex::m3_mul(c0, c1, c2, d));
 }
 
-PTB_HD float qbyte(uint32_t w, int k) { return (float)((w >> (8 * k)) & 0xffu); }
+// Byte k of w as the float 2^23 + 256*byte: one byte-permute places the byte in mantissa bits 8..15 of 0x4B000000
+// (no integer-to-float conversion); the 2^23 bias and the factor 256 are folded into the plane equations below.
+PTB_HD float qbyte_biased(uint32_t w, int k)
+{
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7504u | ((uint32_t)k << 4)));
+#else
+    return ex::from_bits(0x4B000000u | (((w >> (8 * k)) & 0xffu) << 8));
+#endif
+}
 
 // XOR-permute two packed 8-bit masks (bits 0..7 and 8..15): bit (s ^ x) of the result = bit s of the input
 PTB_HD uint32_t xor_permute16(uint32_t m, uint32_t x)
@@ -81,17 +91,25 @@ PTB_HD uint32_t xor_permute16(uint32_t m, uint32_t x)
     return m;
 }
 
-// Conservative test of the 8 quantised child boxes of one node; returns the hit mask by slot.
+// Conservative test of the 8 quantised child boxes of one node; returns a hit mask by slot (bits of empty slots are
+// meaningless: the caller masks with imask | lmask).
+// Plane distance t = (p + q*2^e - o) * idq = q*s + b with s = 2^e*idq, b = (p - o)*idq, evaluated as one FMA per plane:
+// t = v*s8 + c where v = 2^23 + 256*q (qbyte_biased), s8 = s/256, c = b - 2^15*s.
 PTB_HD uint32_t wide_node_test(const uint4& q0, const uint4& q2, const uint4& q3, const uint4& q4, const TravRay& r, float t_max)
 {
     const float px = ex::from_bits(q0.x), py = ex::from_bits(q0.y), pz = ex::from_bits(q0.z);
     const float sx0 = ex::from_bits((q0.w & 0xffu) << 23), sy0 = ex::from_bits(((q0.w >> 8) & 0xffu) << 23), sz0 = ex::from_bits(((q0.w >> 16) & 0xffu) << 23);
     const float sx = sx0 * r.idq.x, sy = sy0 * r.idq.y, sz = sz0 * r.idq.z;
     const float bx = (px - r.o.x) * r.idq.x, by = (py - r.o.y) * r.idq.y, bz = (pz - r.o.z) * r.idq.z;
-    // rounding slack: the fused evaluation below differs from the exact slab arithmetic by a few ulps of |b| + 255|s|
-    const float k = 9.5367432e-7f;  // 2^-20
-    const float ex_ = (fabsf(bx) + 255.0f * fabsf(sx)) * k, ey_ = (fabsf(by) + 255.0f * fabsf(sy)) * k, ez_ = (fabsf(bz) + 255.0f * fabsf(sz)) * k;
-    const float bnx = bx - ex_, bfx = bx + ex_, bny = by - ey_, bfy = by + ey_, bnz = bz - ez_, bfz = bz + ez_;
+    // rounding slack: the fused evaluation differs from the exact slab arithmetic by a few ulps of |b| + 255|s|, plus the
+    // rounding of the bias term c (<= 2^-9 |s|)
+    const float k = 9.5367432e-7f, kb = 7.8125e-3f;  // 2^-20, 2^-7
+    const float ex_ = fmaf(fabsf(bx) + 255.0f * fabsf(sx), k, fabsf(sx) * kb), ey_ = fmaf(fabsf(by) + 255.0f * fabsf(sy), k, fabsf(sy) * kb),
+                ez_ = fmaf(fabsf(bz) + 255.0f * fabsf(sz), k, fabsf(sz) * kb);
+    const float bias = -32768.0f, inv256 = 0.00390625f;
+    const float cnx = fmaf(bias, sx, bx - ex_), cfx = fmaf(bias, sx, bx + ex_), cny = fmaf(bias, sy, by - ey_), cfy = fmaf(bias, sy, by + ey_),
+                cnz = fmaf(bias, sz, bz - ez_), cfz = fmaf(bias, sz, bz + ez_);
+    const float s8x = sx * inv256, s8y = sy * inv256, s8z = sz * inv256;
     // near/far byte planes by direction sign
     const bool nx = r.idq.x < 0.0f, ny = r.idq.y < 0.0f, nz = r.idq.z < 0.0f;
     const uint32_t lox0 = q2.x, lox1 = q2.y, loy0 = q2.z, loy1 = q2.w, loz0 = q3.x, loz1 = q3.y;
@@ -103,16 +121,14 @@ PTB_HD uint32_t wide_node_test(const uint4& q0, const uint4& q2, const uint4& q3
 #pragma unroll
     for (int s = 0; s < 8; ++s)
     {
-        const int kb = s & 3;
+        const int b4 = s & 3;
         const uint32_t wnx = s < 4 ? nx0 : nx1, wfx = s < 4 ? fx0 : fx1, wny = s < 4 ? ny0 : ny1, wfy = s < 4 ? fy0 : fy1, wnz = s < 4 ? nz0 : nz1, wfz = s < 4 ? fz0 : fz1;
-        // an empty slot has lo=255 > hi=0 on every axis: whichever is "near" the interval is empty for any direction
-        const uint32_t lo_b = ((s < 4 ? lox0 : lox1) >> (8 * kb)) & 0xffu, hi_b = ((s < 4 ? hix0 : hix1) >> (8 * kb)) & 0xffu;
-        const float tnx = fmaf(qbyte(wnx, kb), sx, bnx), tfx = fmaf(qbyte(wfx, kb), sx, bfx);
-        const float tny = fmaf(qbyte(wny, kb), sy, bny), tfy = fmaf(qbyte(wfy, kb), sy, bfy);
-        const float tnz = fmaf(qbyte(wnz, kb), sz, bnz), tfz = fmaf(qbyte(wfz, kb), sz, bfz);
+        const float tnx = fmaf(qbyte_biased(wnx, b4), s8x, cnx), tfx = fmaf(qbyte_biased(wfx, b4), s8x, cfx);
+        const float tny = fmaf(qbyte_biased(wny, b4), s8y, cny), tfy = fmaf(qbyte_biased(wfy, b4), s8y, cfy);
+        const float tnz = fmaf(qbyte_biased(wnz, b4), s8z, cnz), tfz = fmaf(qbyte_biased(wfz, b4), s8z, cfz);
         const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, ex::EPS));
         const float tf = fminf(fminf(tfx, tfy), fminf(tfz, t_max));
-        if (tn <= tf && lo_b <= hi_b) mask |= (1u << s);
+        if (tn <= tf) mask |= (1u << s);
     }
     return mask;
 }
@@ -133,161 +149,250 @@ PTB_HD void finish_hit(const SceneDev& S, V3 d_world, uint32_t inst, uint32_t pr
 }
 
 // ------------------------------------------------------------------------------------------------------------------------
-// 8-wide traversal.  Stack entries (uint2): x = child_base | leaf header index, y = kind/payload:
+// 8-wide traversal as a resumable per-ray state machine.  Stack entries (uint2): x = child_base | leaf header index,
+// y = kind/payload:
 //   group   : y = hits_permuted (bits 0..7) | imask << 8            (bit 31 clear)
 //   instance: y = 0x80000000                                          x = leaf header index of a TLAS leaf
+// One wide_step() lets a ray flow through up to four stages, each at a single code location so that the lanes of a warp
+// that need the same stage execute it together:  P (pop / descend / enter instance) -> N (fetch + test one wide node)
+// -> L (one reference leaf: exact box, exact t_enter) -> T (one triangle).  Leaves of a BLAS node are finished (front to
+// back) before its inner children are visited, TLAS leaves are stacked nearest-on-top: the visit order is that of the
+// nested-loop formulation this replaces.
 // ------------------------------------------------------------------------------------------------------------------------
+constexpr uint32_t TRAV_NONE = 0xffffffffu;
+struct WideTrav
+{
+    V3 ow, dw, invw;    // world-space ray and its exact inv_direction (ray.rs:1-8)
+    uint32_t oiw;
+    TravRay ray;        // current space: world, or BLAS space after Ray::transform
+    float t_max;        // closest-hit: current nearest t (tlas.rs:96 / blas.rs:236,247)
+    uint32_t node;      // wide node to fetch next, or TRAV_NONE
+    uint2 G;            // inner children of the current node still to visit
+    int sp, blas_sp;
+    uint32_t cur_inst;  // InstanceRow index while inside a BLAS, TRAV_NONE in the TLAS
+    uint32_t lh;        // BLAS node: hit leaves still to process (permuted order, highest bit = nearest)
+    uint32_t lmask, leaf_base;
+    uint32_t tri_i, tri_end;  // triangle slots of the current leaf still to test
+    float t_enter;
+    float hit_u, hit_v;
+    uint32_t hit_slot, hit_inst;  // hit_inst == TRAV_NONE: nothing found yet
+    uint32_t any;       // any-hit query (TLAS::any_intersect) — used when the step is instantiated with MODE == 2
+};
+
+PTB_HD void wide_begin(WideTrav& s, const SceneDev& S, int which, V3 o, V3 d, float t_max, bool any)
+{
+    s.ow = o;
+    s.dw = d;
+    set_ray(s.ray, o, d);
+    s.invw = s.ray.inv;
+    s.oiw = s.ray.oi;
+    s.t_max = t_max;
+    s.node = S.tlas[which].wide_root;
+    s.G.x = 0;
+    s.G.y = 0;
+    s.sp = 0;
+    s.blas_sp = 0;
+    s.cur_inst = TRAV_NONE;
+    s.lh = 0;
+    s.lmask = 0;
+    s.leaf_base = 0;
+    s.tri_i = 0;
+    s.tri_end = 0;
+    s.t_enter = 0.0f;
+    s.hit_u = s.hit_v = 0.0f;
+    s.hit_slot = 0;
+    s.hit_inst = TRAV_NONE;
+    s.any = any ? 1u : 0u;
+}
+
+PTB_HD int hi_bit(uint32_t m)
+{
+#if defined(__CUDA_ARCH__)
+    return 31 - __clz((int)m);
+#else
+    return 31 - __builtin_clz(m);
+#endif
+}
+PTB_HD int lo_bit(uint32_t m)
+{
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)m) - 1;
+#else
+    return __builtin_ctz(m);
+#endif
+}
+PTB_HD uint32_t popc32(uint32_t m)
+{
+#if defined(__CUDA_ARCH__)
+    return (uint32_t)__popc(m);
+#else
+    return (uint32_t)__builtin_popcount(m);
+#endif
+}
+
+// MODE 0: closest hit, 1: any hit, 2: s.any decides at run time.  Returns false when the traversal is complete
+// (closest: s.hit_inst != TRAV_NONE tells whether something was hit; any: s.hit_inst != TRAV_NONE == occluded).
+// wide_step_pop: stage P.  Returns false when the traversal is complete (stack empty, nothing pending).
+PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, uint2* stack)
+{
+    // ---- P: nothing pending -> next node from the current group, or pop ----------------------------------------------
+    if (s.tri_i >= s.tri_end && s.lh == 0u && s.node == TRAV_NONE)
+    {
+        if (s.G.y == 0u)
+        {
+            if (s.cur_inst != TRAV_NONE && s.sp == s.blas_sp)
+            {
+                s.cur_inst = TRAV_NONE;  // leave the instance: back to the world ray
+                s.ray.o = s.ow;
+                s.ray.d = s.dw;
+                s.ray.inv = s.invw;
+                s.ray.idq = ex::v3(finite_recip_of(s.invw.x), finite_recip_of(s.invw.y), finite_recip_of(s.invw.z));
+                s.ray.oi = s.oiw;
+            }
+            if (s.sp == 0) return false;
+            const uint2 e = stack[--s.sp];
+            if (e.y & 0x80000000u)
+            {
+                // TLAS leaf (tlas.rs:88-100 / :132-139): exact leaf box with the current t_max, then Ray::transform
+                const float4 h0 = PTB_LDG4F(S.leaf_headers + (size_t)e.x * 2), h1 = PTB_LDG4F(S.leaf_headers + (size_t)e.x * 2 + 1);
+                float t_enter;
+                if (ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), s.ray.o, s.ray.inv, s.t_max, &t_enter))
+                {
+                    s.cur_inst = ex::bits(h1.w);
+                    const float4* ip = (const float4*)S.inst[s.cur_inst].inv;
+                    const float4 i0 = PTB_LDG4F(ip), i1 = PTB_LDG4F(ip + 1), i2 = PTB_LDG4F(ip + 2);
+                    const float inv12[12] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w, i2.x, i2.y, i2.z, i2.w};
+                    transform_ray(s.ray, s.ow, s.dw, inv12);
+                    s.blas_sp = s.sp;
+                    s.node = PTB_LDGU(&S.inst[s.cur_inst].wide_root);
+                }
+            }
+            else s.G = e;
+        }
+        if (s.node == TRAV_NONE && s.G.y)
+        {
+            // descend into the nearest remaining child of the current group
+            const uint32_t ih = s.G.y & 0xffu, imask = (s.G.y >> 8) & 0xffu;
+            const int p = hi_bit(ih);
+            const uint32_t sl = (uint32_t)p ^ s.ray.oi;
+            s.node = s.G.x + popc32(imask & ((1u << sl) - 1u));
+            s.G.y &= ~(1u << p);
+            if (s.G.y & 0xffu) stack[s.sp++] = s.G;
+            s.G.y = 0u;
+        }
+    }
+    return true;
+}
+PTB_HD bool wide_wants_node(const WideTrav& s) { return s.node != TRAV_NONE; }
+PTB_HD bool wide_has_leaf_work(const WideTrav& s) { return s.lh != 0u || s.tri_i < s.tri_end; }
+
+// wide_step_work: stages N, L, T.  `allow_node` lets a warp postpone the (expensive) node stage until enough of its lanes
+// want it (persist.cuh); a lane whose node is postponed simply keeps it pending.  Returns false when an any-hit query is
+// decided.
+template <int MODE>
+PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, uint2* stack, bool allow_node)
+{
+    const bool ANY = MODE == 2 ? (s.any != 0u) : (MODE == 1);
+    // ---- N: fetch and test one wide node ---------------------------------------------------------------------------------
+    if (allow_node && s.node != TRAV_NONE)
+    {
+        const uint4* np = S.wide + (size_t)s.node * 5;
+        const uint4 q0 = PTB_LDG4U(np), q1 = PTB_LDG4U(np + 1), q2 = PTB_LDG4U(np + 2), q3 = PTB_LDG4U(np + 3), q4 = PTB_LDG4U(np + 4);
+        s.node = TRAV_NONE;
+        const uint32_t hits = wide_node_test(q0, q2, q3, q4, s.ray, s.t_max);
+        const uint32_t imask = q0.w >> 24, lmask = q1.z & 0xffu;
+        const uint32_t perm = xor_permute16((hits & imask) | ((hits & lmask) << 8), s.ray.oi);
+        const uint32_t ih = perm & 0xffu, lh = (perm >> 8) & 0xffu;
+        s.G.x = q1.x;
+        s.G.y = ih ? (ih | (imask << 8)) : 0u;
+        if (s.cur_inst != TRAV_NONE)
+        {
+            s.lh = lh;  // triangle leaves: processed front to back before any inner child
+            s.lmask = lmask;
+            s.leaf_base = q1.y;
+        }
+        else
+        {
+            // TLAS leaves: push the inner group first, then the instances far to near (nearest popped first)
+            if (s.G.y) { stack[s.sp++] = s.G; s.G.y = 0u; }
+            uint32_t m = lh;
+            while (m)
+            {
+                const int p = lo_bit(m);
+                m &= m - 1u;
+                const uint32_t sl = (uint32_t)p ^ s.ray.oi;
+                uint2 e;
+                e.x = q1.y + popc32(lmask & ((1u << sl) - 1u));
+                e.y = 0x80000000u;
+                stack[s.sp++] = e;
+            }
+        }
+    }
+    // ---- L: one reference leaf of the current BLAS node -------------------------------------------------------------------
+    if (s.tri_i >= s.tri_end && s.lh)
+    {
+        const int p = hi_bit(s.lh);
+        s.lh &= ~(1u << p);
+        const uint32_t sl = (uint32_t)p ^ s.ray.oi;
+        const uint32_t hidx = s.leaf_base + popc32(s.lmask & ((1u << sl) - 1u));
+        const float4 h0 = PTB_LDG4F(S.leaf_headers + (size_t)hidx * 2), h1 = PTB_LDG4F(S.leaf_headers + (size_t)hidx * 2 + 1);
+        const uint32_t cw = ex::bits(h0.w);
+        float t_enter = 0.0f;
+        bool go = true;
+        // blas.rs:137-138 / :264 — exact reference leaf box, exact entry distance (the BLAS root is entered untested with
+        // t_estimate = 0 by the closest-hit query, blas.rs:217)
+        if (ANY || !(cw & LEAF_ROOT_FLAG)) go = ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), s.ray.o, s.ray.inv, s.t_max, &t_enter);
+        if (go)
+        {
+            s.tri_i = ex::bits(h1.w);
+            s.tri_end = s.tri_i + (cw & ~LEAF_ROOT_FLAG);
+            s.t_enter = t_enter;
+        }
+    }
+    // ---- T: one triangle ---------------------------------------------------------------------------------------------------
+    if (s.tri_i < s.tri_end)
+    {
+        const float4* pp = S.tri_planes + (size_t)s.tri_i * 3;
+        const float4 a = PTB_LDG4F(pp), b = PTB_LDG4F(pp + 1), c = PTB_LDG4F(pp + 2);
+        const float n0[4] = {a.x, a.y, a.z, a.w}, n1[4] = {b.x, b.y, b.z, b.w}, n2[4] = {c.x, c.y, c.z, c.w};
+        if (ANY)
+        {
+            if (ex::tri_hit_bool(n0, n1, n2, s.ray.o, s.ray.d, s.t_max, s.t_enter))
+            {
+                s.hit_inst = s.cur_inst;
+                return false;
+            }
+        }
+        else
+        {
+            float t, u, v;
+            if (ex::tri_hit(n0, n1, n2, s.ray.o, s.ray.d, s.t_max, s.t_enter, &t, &u, &v))
+            {
+                s.t_max = t;
+                s.hit_u = u; s.hit_v = v; s.hit_slot = s.tri_i; s.hit_inst = s.cur_inst;
+            }
+        }
+        ++s.tri_i;
+    }
+    return true;
+}
+
+template <int MODE>
+PTB_HD bool wide_step(WideTrav& s, const SceneDev& S, uint2* stack)
+{
+    return wide_step_pop(s, S, stack) && wide_step_work<MODE>(s, S, stack, true);
+}
+
 template <bool ANY>
 PTB_HD bool wide_traverse(const SceneDev& S, int which, V3 o_world, V3 d_world, float t_max, Hit* hit)
 {
     uint2 stack[WIDE_STACK_CAP];
-    int sp = 0;
-    TravRay ray;
-    set_ray(ray, o_world, d_world);
-    bool in_blas = false;
-    int blas_sp = 0;
-    uint32_t cur_inst = 0xffffffffu;
-    uint32_t node = S.tlas[which].wide_root;
-    uint2 G;
-    G.x = 0;
-    G.y = 0;
-    bool found = false;
-    const uint32_t NONE = 0xffffffffu;
-    for (;;)
-    {
-        if (node != NONE)
-        {
-            const uint4* np = S.wide + (size_t)node * 5;
-            const uint4 q0 = PTB_LDG4U(np), q1 = PTB_LDG4U(np + 1), q2 = PTB_LDG4U(np + 2), q3 = PTB_LDG4U(np + 3), q4 = PTB_LDG4U(np + 4);
-            node = NONE;
-            const uint32_t hits = wide_node_test(q0, q2, q3, q4, ray, t_max);
-            const uint32_t imask = q0.w >> 24, lmask = q1.z & 0xffu;
-            const uint32_t perm = xor_permute16((hits & imask) | ((hits & lmask) << 8), ray.oi);
-            const uint32_t ih = perm & 0xffu;
-            uint32_t lh = (perm >> 8) & 0xffu;
-            if (ih) { G.x = q1.x; G.y = ih | (imask << 8); }
-            else G.y = 0;
-            if (in_blas)
-            {
-                // triangle leaves: front to back, right now
-                while (lh)
-                {
-#if defined(__CUDA_ARCH__)
-                    const int p = 31 - __clz((int)lh);
-#else
-                    const int p = 31 - __builtin_clz(lh);
-#endif
-                    lh &= ~(1u << p);
-                    const uint32_t s = (uint32_t)p ^ ray.oi;
-#if defined(__CUDA_ARCH__)
-                    const uint32_t hidx = q1.y + __popc(lmask & ((1u << s) - 1u));
-#else
-                    const uint32_t hidx = q1.y + __builtin_popcount(lmask & ((1u << s) - 1u));
-#endif
-                    const float4 h0 = PTB_LDG4F(S.leaf_headers + (size_t)hidx * 2), h1 = PTB_LDG4F(S.leaf_headers + (size_t)hidx * 2 + 1);
-                    const uint32_t cw = ex::bits(h0.w);
-                    float t_enter = 0.0f;
-                    if (ANY || !(cw & LEAF_ROOT_FLAG))
-                    {
-                        // blas.rs:137-138 / :264 — exact reference leaf box, exact entry distance
-                        if (!ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), ray.o, ray.inv, t_max, &t_enter)) continue;
-                    }
-                    const uint32_t cnt = cw & ~LEAF_ROOT_FLAG, first = ex::bits(h1.w);
-                    for (uint32_t k = 0; k < cnt; ++k)
-                    {
-                        const float4* pp = S.tri_planes + (size_t)(first + k) * 3;
-                        const float4 a = PTB_LDG4F(pp), b = PTB_LDG4F(pp + 1), c = PTB_LDG4F(pp + 2);
-                        const float n0[4] = {a.x, a.y, a.z, a.w}, n1[4] = {b.x, b.y, b.z, b.w}, n2[4] = {c.x, c.y, c.z, c.w};
-                        if (ANY)
-                        {
-                            if (ex::tri_hit_bool(n0, n1, n2, ray.o, ray.d, t_max, t_enter)) return true;
-                        }
-                        else
-                        {
-                            float t, u, v;
-                            if (ex::tri_hit(n0, n1, n2, ray.o, ray.d, t_max, t_enter, &t, &u, &v))
-                            {
-                                t_max = t;
-                                hit->t = t; hit->u = u; hit->v = v; hit->slot_or_prim = first + k; hit->inst = cur_inst;
-                                found = true;
-                            }
-                        }
-                    }
-                }
-            }
-            else
-            {
-                // TLAS leaves: push the inner group first, then the instances far to near (nearest popped first)
-                if (G.y) { stack[sp++] = G; G.y = 0; }
-                uint32_t m = lh;
-                while (m)
-                {
-#if defined(__CUDA_ARCH__)
-                    const int p = __ffs((int)m) - 1;
-#else
-                    const int p = __builtin_ctz(m);
-#endif
-                    m &= m - 1;
-                    const uint32_t s = (uint32_t)p ^ ray.oi;
-#if defined(__CUDA_ARCH__)
-                    const uint32_t hidx = q1.y + __popc(lmask & ((1u << s) - 1u));
-#else
-                    const uint32_t hidx = q1.y + __builtin_popcount(lmask & ((1u << s) - 1u));
-#endif
-                    uint2 e;
-                    e.x = hidx;
-                    e.y = 0x80000000u;
-                    stack[sp++] = e;
-                }
-            }
-        }
-        if (G.y)
-        {
-            // descend into the nearest remaining child of the current group
-            const uint32_t ih = G.y & 0xffu, imask = (G.y >> 8) & 0xffu;
-#if defined(__CUDA_ARCH__)
-            const int p = 31 - __clz((int)ih);
-#else
-            const int p = 31 - __builtin_clz(ih);
-#endif
-            const uint32_t s = (uint32_t)p ^ ray.oi;
-#if defined(__CUDA_ARCH__)
-            node = G.x + __popc(imask & ((1u << s) - 1u));
-#else
-            node = G.x + __builtin_popcount(imask & ((1u << s) - 1u));
-#endif
-            G.y &= ~(1u << p);
-            if (G.y & 0xffu) stack[sp++] = G;
-            G.y = 0;
-            continue;
-        }
-        // current group exhausted
-        if (in_blas && sp == blas_sp)
-        {
-            in_blas = false;  // leave the instance: back to the world ray
-            set_ray(ray, o_world, d_world);
-        }
-        if (sp == 0) break;
-        const uint2 e = stack[--sp];
-        if (e.y & 0x80000000u)
-        {
-            // TLAS leaf (tlas.rs:88-100 / :132-139): exact leaf box with the current t_max, then Ray::transform
-            const float4 h0 = PTB_LDG4F(S.leaf_headers + (size_t)e.x * 2), h1 = PTB_LDG4F(S.leaf_headers + (size_t)e.x * 2 + 1);
-            float t_enter;
-            if (!ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), ray.o, ray.inv, t_max, &t_enter)) continue;
-            cur_inst = ex::bits(h1.w);
-            const InstanceRow& R = S.inst[cur_inst];
-            float inv12[12];
-#pragma unroll
-            for (int k = 0; k < 12; ++k) inv12[k] = PTB_LDGF(R.inv + k);
-            transform_ray(ray, o_world, d_world, inv12);
-            in_blas = true;
-            blas_sp = sp;
-            node = PTB_LDGU(&R.wide_root);
-        }
-        else G = e;
-    }
-    return found;
+    WideTrav s;
+    wide_begin(s, S, which, o_world, d_world, t_max, ANY);
+    while (wide_step<ANY ? 1 : 0>(s, S, stack)) {}
+    if (s.hit_inst == TRAV_NONE) return false;
+    if (!ANY) { hit->t = s.t_max; hit->u = s.hit_u; hit->v = s.hit_v; hit->slot_or_prim = s.hit_slot; hit->inst = s.hit_inst; }
+    return true;
 }
 
 // ------------------------------------------------------------------------------------------------------------------------

@@ -374,6 +374,26 @@ PTB_HD void shadow_contrib_t(const RenderView& V, uint32_t slot, V3 o, float4* r
     r->x += c.x; r->y += c.y; r->z += c.z;
 }
 
+// contribution of a light found by the BSDF-sampled probe and visible from the hit point (integrator.rs:105-123)
+PTB_HD V3 probe_light_contrib(const RenderView& V, uint32_t slot, V3 d, float tl, float u, float v, uint32_t prim, uint32_t inst)
+{
+    V3 ln;
+    bool ff;
+    finish_hit(V.S, d, inst, prim, u, v, &ln, &ff);
+    const InstanceRow& R = V.S.inst[inst];
+    const Mat lmat = load_mat(V.S.mat, R.blas);
+    // get_sample_pdf(light, material) / light.area()  (light_sampler.rs:39, integrator.rs:111)
+    const float4 n0 = V.S.planes_by_prim[(size_t)(R.tri_base + prim) * 3];
+    const float area = 0.5f * sqrtf((n0.x * n0.x + n0.y * n0.y) + n0.z * n0.z);
+    const float sample_pdf = (area * sqrtf(dot(lmat.colour, lmat.colour)) / V.S.light_max) / area;
+    const float cosine = fabsf(dot(d, ln));
+    const float light_pdf = sample_pdf * (tl * tl / cosine);
+    const float bp = V.probe[slot].d.w;
+    const float wgt = (bp * bp) / (bp * bp + light_pdf * light_pdf);  // mis_heuristic<2>(bsdf_pdf, light_pdf)
+    const float4 f = V.probe[slot].f;
+    return ex::v3(lmat.colour.x * wgt * f.x, lmat.colour.y * wgt * f.y, lmat.colour.z * wgt * f.z);
+}
+
 // ---- probe ---------------------------------------------------------------------------------------------------------------
 // returns 1 when the lights-TLAS probe hit a light and a world shadow ray was traced
 template <bool BIN>
@@ -390,21 +410,8 @@ PTB_HD uint32_t probe_contrib_t(const RenderView& V, uint32_t slot, V3 o, float4
     const bool occluded = BIN ? bin_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy) : wide_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy);  // :103
     if (occluded) return 1u;
     const uint32_t prim = BIN ? h.slot_or_prim : V.S.tri_prim[h.slot_or_prim];
-    V3 ln;
-    bool ff;
-    finish_hit(V.S, d, h.inst, prim, h.u, h.v, &ln, &ff);
-    const InstanceRow& R = V.S.inst[h.inst];
-    const Mat lmat = load_mat(V.S.mat, R.blas);
-    // get_sample_pdf(light, material) / light.area()  (light_sampler.rs:39, integrator.rs:111)
-    const float4 n0 = V.S.planes_by_prim[(size_t)(R.tri_base + prim) * 3];
-    const float area = 0.5f * sqrtf((n0.x * n0.x + n0.y * n0.y) + n0.z * n0.z);
-    const float sample_pdf = (area * sqrtf(dot(lmat.colour, lmat.colour)) / V.S.light_max) / area;
-    const float cosine = fabsf(dot(d, ln));
-    const float light_pdf = sample_pdf * (tl * tl / cosine);
-    const float bp = d4.w;
-    const float wgt = (bp * bp) / (bp * bp + light_pdf * light_pdf);  // mis_heuristic<2>(bsdf_pdf, light_pdf)
-    const float4 f = V.probe[slot].f;
-    r->x += lmat.colour.x * wgt * f.x; r->y += lmat.colour.y * wgt * f.y; r->z += lmat.colour.z * wgt * f.z;
+    const V3 c = probe_light_contrib(V, slot, d, tl, h.u, h.v, prim, h.inst);
+    r->x += c.x; r->y += c.y; r->z += c.z;
     return 1u;
 }
 
