@@ -118,6 +118,7 @@ def main():
     import torch
     import torch.distributed as dist
     import path_tracer_b200 as ptb
+    from path_tracer_b200 import multi
 
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
@@ -149,11 +150,11 @@ def main():
     def step(index, e2e):
         if e2e:
             ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, sd.aspect)  # the per-frame input of the seam (main.rs:199)
-        ctx.frame_begin(W, H)
-        # weak scaling: rank r renders the global samples [ (index*world + r) * spp, +spp )
-        ctx.render((index * world + rank) * spp, spp, seed=args.seed, max_bounces=sd.max_bounces)
+        ctx.frame_begin(W, H)  # clears the bound accumulation buffer
+        # weak scaling: step `index` covers the global samples [index*world*spp, +world*spp); rank r renders its block of spp,
+        # then ONE NCCL reduce of the accumulation buffer onto rank 0 (NVLink)
+        multi.render_partitioned(lambda first, n: ctx.render(first, n, seed=args.seed, max_bounces=sd.max_bounces), acc, index * world * spp, world * spp, rank, world)
         if world > 1:
-            dist.reduce(acc, dst=0)  # one NCCL reduce of the accumulation buffer per frame (NVLink)
             torch.cuda.synchronize()
         if e2e and rank == 0:
             ctx.read_accum(h_acc)
