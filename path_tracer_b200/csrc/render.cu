@@ -53,7 +53,10 @@ constexpr uint32_t POLL_RING = 8192;
 struct RenderState
 {
     uint32_t W = 0, H = 0, npix = 0;
-    DBuf<float4> accum_own, accum_sq, position;
+    DBuf<float4> accum_own, accum_sq, position;   // per pixel
+    DBuf<float4> s_accum, s_accum_sq, s_position;  // per slot (K slots per pixel)
+    DBuf<uint32_t> s_id;
+    uint32_t n_slots = 0;
     DBuf<RayRec> ray;
     DBuf<PathRec> path;
     DBuf<HitRec> hit;
@@ -108,17 +111,53 @@ __device__ __forceinline__ bool fetch_chunk(uint32_t* cursor, uint32_t nchunks, 
     return c < nchunks;
 }
 
-__global__ void __launch_bounds__(128) k_init(RenderView V, Queues Q)
+__global__ void __launch_bounds__(128) k_init(RenderView V, Queues Q, const uint32_t* id_px)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= Q.npix) return;
+    if (i >= Q.npix) return;  // Q.npix = number of slots
     V.ray[i].o.w = 0.0f;  // no sample in flight
     V.ray[i].d.w = 0.0f;  // samples started = 0
+    V.accum[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (V.accum_sq) V.accum_sq[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    V.id[i] = V.K == 1u ? id_px[i] : 0u;  // one slot per pixel: the slot continues the pixel's id history (main.rs:206)
     Q.term[0][i] = i;
     if (i == 0)
     {
         for (int s = 0; s < 3; ++s) Q.c->set[s] = WfSet{};
         Q.c->set[0].n_term = Q.npix;
+    }
+}
+
+// Fold the K per-slot partial results of every pixel into the per-pixel outputs, in slot order (deterministic):
+// accum += sum_k accum_k (accumulate.wgsl:23); position / id of the LAST sample, id history shifted as main.rs:206.
+__global__ void __launch_bounds__(256) k_combine(RenderView V, float4* accum_px, float4* accum_sq_px, float4* position_px, uint32_t* id_px, uint32_t sample_count)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= V.npix) return;
+    float4 a = accum_px[p];
+    for (uint32_t k = 0; k < V.K; ++k)
+    {
+        const float4 b = V.accum[(size_t)k * V.npix + p];
+        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    accum_px[p] = a;
+    if (accum_sq_px)
+    {
+        float4 q = accum_sq_px[p];
+        for (uint32_t k = 0; k < V.K; ++k)
+        {
+            const float4 b = V.accum_sq[(size_t)k * V.npix + p];
+            q.x += b.x; q.y += b.y; q.z += b.z; q.w += b.w;
+        }
+        accum_sq_px[p] = q;
+    }
+    const uint32_t k_last = (sample_count - 1u) % V.K;
+    position_px[p] = V.position[(size_t)k_last * V.npix + p];
+    if (V.K == 1u) id_px[p] = V.id[p];
+    else
+    {
+        const uint32_t k_prev = (sample_count - 2u) % V.K;  // K <= sample_count, so sample_count >= 2 here
+        id_px[p] = ((V.id[(size_t)k_prev * V.npix + p] & 0xffffu) << 16) | (V.id[(size_t)k_last * V.npix + p] & 0xffffu);
     }
 }
 
@@ -462,6 +501,7 @@ void render_state_destroy(ptb_context* ctx)
     if (rs->ev_end) cudaEventDestroy(rs->ev_end);
     if (rs->h_flags) cudaFreeHost(rs->h_flags);
     rs->accum_own.release(); rs->accum_sq.release(); rs->position.release();
+    rs->s_accum.release(); rs->s_accum_sq.release(); rs->s_position.release(); rs->s_id.release();
     rs->ray.release(); rs->path.release(); rs->hit.release(); rs->shadow.release(); rs->probe.release();
     DBuf<uint32_t>* u32s[] = {&rs->id, &rs->q_cont0, &rs->q_cont1, &rs->q_term0, &rs->q_term1, &rs->q_mat, &rs->q_nee};
     for (auto* b : u32s) b->release();
@@ -563,7 +603,7 @@ int ptb_enable_second_moment(ptb_context* ctx, int enable)
 int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height)
 {
     REQUIRE_DEVICE(ctx);
-    if (width == 0 || height == 0 || (uint64_t)width * height > (uint64_t)NEE_SLOT_MASK) return ctx->fail(PTB_ERR_INVALID, "bad frame size");
+    if (width == 0 || height == 0 || (uint64_t)width * height > (uint64_t)NEE_SLOT_MASK / 8u) return ctx->fail(PTB_ERR_INVALID, "bad frame size");
     PTB_CUDA(ctx, cudaSetDevice(ctx->device));
     const bool fresh = ctx->rs == nullptr;
     if (fresh) ctx->rs = new RenderState();
@@ -574,16 +614,8 @@ int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height)
     rs.W = width; rs.H = height; rs.npix = npix;
     PTB_CUDA(ctx, rs.accum_own.resize(npix));
     PTB_CUDA(ctx, rs.position.resize(npix));
-    PTB_CUDA(ctx, rs.ray.resize(npix));
-    PTB_CUDA(ctx, rs.path.resize(npix));
-    PTB_CUDA(ctx, rs.hit.resize(npix));
-    PTB_CUDA(ctx, rs.shadow.resize(npix));
-    PTB_CUDA(ctx, rs.probe.resize(npix));
+    PTB_CUDA(ctx, rs.id.resize(npix));
     if (ctx->second_moment) PTB_CUDA(ctx, rs.accum_sq.resize(npix));
-    DBuf<uint32_t>* u32s[] = {&rs.id, &rs.q_cont0, &rs.q_cont1, &rs.q_term0, &rs.q_term1, &rs.q_nee};
-    for (auto* b : u32s) PTB_CUDA(ctx, b->resize(npix));
-    PTB_CUDA(ctx, rs.q_mat.resize((size_t)npix * 7));
-    PTB_CUDA(ctx, rs.volset.resize(npix));
     PTB_CUDA(ctx, rs.counters.resize(1));
     if (!rs.h_flags) PTB_CUDA(ctx, cudaHostAlloc((void**)&rs.h_flags, POLL_RING * 2 * sizeof(uint32_t), cudaHostAllocDefault));
     if (!rs.ev_begin) { PTB_CUDA(ctx, cudaEventCreate(&rs.ev_begin)); PTB_CUDA(ctx, cudaEventCreate(&rs.ev_end)); }
@@ -626,24 +658,46 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     if (sample_count == 0) return PTB_OK;
     PTB_CUDA(ctx, cudaSetDevice(ctx->device));
     RenderState& rs = *ctx->rs;
+    // K slots per pixel (never more than samples, so every slot renders at least one)
+    const uint32_t K = std::max(1u, std::min<uint32_t>(std::min<uint32_t>((uint32_t)std::max(1, ctx->opt_slots_per_pixel), 8u), sample_count));
+    const size_t n_slots = (size_t)rs.npix * K;
+    if (n_slots > (size_t)NEE_SLOT_MASK) return ctx->fail(PTB_ERR_UNSUPPORTED, "too many path slots");
+    PTB_CUDA(ctx, rs.s_accum.resize(n_slots));
+    PTB_CUDA(ctx, rs.s_position.resize(n_slots));
+    PTB_CUDA(ctx, rs.s_id.resize(n_slots));
+    if (ctx->second_moment) PTB_CUDA(ctx, rs.s_accum_sq.resize(n_slots));
+    PTB_CUDA(ctx, rs.ray.resize(n_slots));
+    PTB_CUDA(ctx, rs.path.resize(n_slots));
+    PTB_CUDA(ctx, rs.hit.resize(n_slots));
+    PTB_CUDA(ctx, rs.shadow.resize(n_slots));
+    PTB_CUDA(ctx, rs.probe.resize(n_slots));
+    {
+        DBuf<uint32_t>* u32s[] = {&rs.q_cont0, &rs.q_cont1, &rs.q_term0, &rs.q_term1, &rs.q_nee};
+        for (auto* b : u32s) PTB_CUDA(ctx, b->resize(n_slots));
+    }
+    PTB_CUDA(ctx, rs.q_mat.resize(n_slots * 7));
+    PTB_CUDA(ctx, rs.volset.resize(n_slots));
+    rs.n_slots = (uint32_t)n_slots;
     RenderView V{};
     V.S = ctx->S;
     V.cam = cam_dev(ctx);
     V.W = rs.W; V.H = rs.H;
+    V.npix = rs.npix;
+    V.K = K;
     V.sample_begin = sample_begin; V.sample_count = sample_count;
     V.seed = seed;
     V.max_bounces = max_bounces;
     V.enable_nee = enable_nee ? 1u : 0u;
     V.extend_kernel = ctx->opt_extend_kernel ? 1u : 0u;
-    V.accum = rs.accum;
-    V.accum_sq = ctx->second_moment ? rs.accum_sq.p : nullptr;
-    V.position = rs.position.p; V.id = rs.id.p;
+    V.accum = rs.s_accum.p;
+    V.accum_sq = ctx->second_moment ? rs.s_accum_sq.p : nullptr;
+    V.position = rs.s_position.p; V.id = rs.s_id.p;
     V.ray = rs.ray.p; V.path = rs.path.p; V.hit = rs.hit.p; V.shadow = rs.shadow.p; V.probe = rs.probe.p;
     V.volset = ctx->scene.volumes.empty() ? nullptr : rs.volset.p;
     Queues Q{};
     Q.cont[0] = rs.q_cont0.p; Q.cont[1] = rs.q_cont1.p; Q.term[0] = rs.q_term0.p; Q.term[1] = rs.q_term1.p;
     Q.mat = rs.q_mat.p; Q.nee = rs.q_nee.p;
-    Q.npix = rs.npix;
+    Q.npix = rs.n_slots;  // queue capacity and stride: one entry per slot
     Q.c = rs.counters.p;
 
     const int threads = 128;
@@ -682,7 +736,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
 
     PTB_CUDA(ctx, cudaEventRecord(rs.ev_begin, st));
     PTB_CUDA(ctx, mark(-1));
-    k_init<<<(rs.npix + threads - 1) / threads, threads, 0, st>>>(V, Q);
+    k_init<<<(rs.n_slots + threads - 1) / threads, threads, 0, st>>>(V, Q, rs.id.p);
     PTB_CUDA(ctx, mark(1));
     rs.launches += 1;
     const bool sort = ctx->opt_sort_materials != 0, bin = V.extend_kernel != 0u;
@@ -746,6 +800,10 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             }
         }
     }
+    k_combine<<<(rs.npix + 255) / 256, 256, 0, st>>>(V, rs.accum, ctx->second_moment ? rs.accum_sq.p : nullptr, rs.position.p, rs.id.p, sample_count);
+    PTB_CUDA(ctx, mark(6));
+    PTB_CUDA(ctx, cudaGetLastError());
+    rs.launches += 1;
     PTB_CUDA(ctx, cudaEventRecord(rs.ev_end, st));
     PTB_CUDA(ctx, cudaEventSynchronize(rs.ev_end));
     float ms = 0;

@@ -9,8 +9,9 @@
 //   shadow : explicit light sample visibility + contribution (integrator.rs:56-70)
 //   probe  : BSDF-sampled direct light: lights-TLAS closest hit, world any-hit, contribution (integrator.rs:100-123)
 //
-// One slot == one pixel; a slot runs its pixel's samples back to back (path regeneration), so accum[pixel] has a single
-// writer and needs no atomics.  Queues between stages are handled by the callers (render.cu on the device, warp-aggregated;
+// A pixel owns K slots (K = 1 in the host emulation); slot k of a pixel runs the samples k, k+K, k+2K, ... of that pixel back
+// to back (path regeneration) and sums them into its own accumulator, so every accumulator has a single writer and needs
+// no atomics; the K partial sums are folded in a fixed order afterwards (deterministic).  Queues between stages are handled by the callers (render.cu on the device, warp-aggregated;
 // tests/hostemu sequentially on the host): the bodies only return flags.
 //
 // Path state lives in HBM as 32-byte records (one DRAM sector each, two 128-bit accesses): a stage that touches a record
@@ -55,17 +56,19 @@ struct RenderView
     SceneDev S;
     CameraDev cam;
     uint32_t W, H;
+    uint32_t npix;           // W * H
+    uint32_t K;              // slots per pixel: slot = k * npix + pixel renders the samples k, k + K, k + 2K, ... of its pixel
     uint32_t sample_begin, sample_count;
     unsigned long long seed;
     uint32_t max_bounces;
     uint32_t enable_nee;
     uint32_t extend_kernel;  // 0 wide, 1 reference-order
-    // per pixel
-    float4* accum;     // (sum rgb, count)
+    // per slot: partial outputs of the slot's own samples, folded into the per-pixel arrays by the combine step
+    float4* accum;     // (sum rgb, count)                                   accumulate.wgsl:23
     float4* accum_sq;  // optional
-    float4* position;  // main.rs:205
-    uint32_t* id;      // main.rs:206
-    // per slot (== pixel)
+    float4* position;  // of the slot's latest sample                        main.rs:205
+    uint32_t* id;      // (id << 16) | first_id over the slot's samples      main.rs:206
+    // per slot: path state
     RayRec* ray;
     PathRec* path;
     HitRec* hit;
@@ -114,15 +117,17 @@ PTB_HD uint32_t regen_slot(const RenderView& V, uint32_t slot, V3* o_out, V3* d_
             V.accum_sq[slot] = q;
         }
     }
-    if (started >= V.sample_count)
+    const uint32_t pixel = slot % V.npix, sub = slot / V.npix;
+    const uint32_t local = sub + started * V.K;  // index of the slot's next sample within this render call
+    if (local >= V.sample_count)
     {
         V.ray[slot].o.w = ex::from_bits(0u);
         return 0u;
     }
     // main.rs:187-199
-    const uint32_t smp = V.sample_begin + started;
-    const uint32_t x = slot % V.W, y = slot / V.W;
-    Rng rng = rng_stream(V.seed, slot, smp);
+    const uint32_t smp = V.sample_begin + local;
+    const uint32_t x = pixel % V.W, y = pixel / V.W;
+    Rng rng = rng_stream(V.seed, pixel, smp);
     const uint32_t jseed = rng_u32(rng);
     float jx, jy;
     ss_sobol(smp == 0u ? 0u : 1u, jseed, &jx, &jy);  // index = c.w as u32: 0 on the first frame, 1 afterwards (main.rs:194,204)

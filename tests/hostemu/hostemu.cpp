@@ -116,7 +116,7 @@ void emu_render(void* h, const float* cam_m16, const float* cam_eye3, uint32_t W
     V.S = host_view(sc);
     std::memcpy(V.cam.m, cam_m16, 64);
     std::memcpy(V.cam.eye, cam_eye3, 12);
-    V.W = W; V.H = H; V.sample_begin = sample_begin; V.sample_count = sample_count; V.seed = seed; V.max_bounces = max_bounces;
+    V.W = W; V.H = H; V.npix = npix; V.K = 1; V.sample_begin = sample_begin; V.sample_count = sample_count; V.seed = seed; V.max_bounces = max_bounces;
     V.enable_nee = enable_nee ? 1u : 0u;
     V.extend_kernel = extend_kernel ? 1u : 0u;
     std::vector<RayRec> ray(npix);
