@@ -152,6 +152,10 @@ int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height);
 int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_bounces, int enable_nee);
 int ptb_read_accum(ptb_context* ctx, float* rgba);
 int ptb_read_aux(ptb_context* ctx, float* position4, uint32_t* id);
+/* Display image of the accumulation buffer, the step after the path: rgb / w (shader.wgsl:63), Uchimura GT tonemap with the
+ * constants of ImageHelper::write_image (image_helper.rs:44; tonemapping.rs:68-96), gamma 1/2.2, * 255 `as u8`.  rgb: W*H*3 bytes.
+ * flip_y != 0 writes the top image row first (the accumulation buffer has row 0 at the bottom, camera.rs:96). */
+int ptb_read_rgb8(ptb_context* ctx, uint8_t* rgb, int flip_y);
 /* Optional second moment (sum of squared sample values) for statistical parity tests; must be enabled before ptb_frame_begin. */
 int ptb_enable_second_moment(ptb_context* ctx, int enable);
 int ptb_read_second_moment(ptb_context* ctx, float* rgba);

@@ -94,6 +94,12 @@ class OracleScene:
             raise ValueError(L.po_last_error().decode())
         self.nblas = len(sd.blas)
 
+    def set_env(self, rgb):
+        """Environment map, linear RGB [H, W, 3] (ImageHelper::load_image output, image_helper.rs:25-33)."""
+        rgb = np.ascontiguousarray(rgb, np.float32)
+        if lib().po_scene_set_env(self.h, rgb.shape[1], rgb.shape[0], _p(rgb)) != 0:
+            raise RuntimeError(lib().po_last_error().decode())
+
     def close(self):
         if self.h:
             lib().po_scene_destroy(C.c_void_p(self.h))
@@ -237,4 +243,13 @@ def camera_rays(origin, target, fov_deg, aspect, st):
 def rng_stream(seed, pixel, sample, n):
     out = np.zeros(n, np.uint32)
     lib().po_rng_stream(C.c_uint64(seed), pixel, sample, n, _p(out))
+    return out
+
+
+def tonemap_rgb8(accum, flip_y=True):
+    """ImageHelper::write_image's conversion (image_helper.rs:44-46) of an accumulation buffer [H,W,4] (sum rgb, count)."""
+    accum = np.ascontiguousarray(accum, np.float32)
+    H, W = accum.shape[:2]
+    out = np.zeros((H, W, 3), np.uint8)
+    lib().po_tonemap_rgb8(_p(accum), W, H, int(flip_y), _p(out))
     return out

@@ -407,6 +407,46 @@ void po_rng_stream(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t n, u
     for (uint32_t i = 0; i < n; ++i) out[i] = r.u32();
 }
 
+// ---- output stage: ImageHelper::write_image (image_helper.rs:37-58) on the normalised accumulation buffer (shader.wgsl:63) ----
+// gt_tonemap restated from image_helper/tonemapping.rs:2-96 (scalar, per channel).
+static float gt_smoothstep_(float x, float e0, float e1)  // tonemapping.rs:39-56
+{
+    if (x < e0) return 0.0f;
+    if (x > e1) return 1.0f;
+    const float a = (x - e0) / (e1 - e0), b = 3.0f - 2.0f * a;
+    return a * a * b;
+}
+static float gt_lerp_(float x, float e0, float e1)  // tonemapping.rs:21-35
+{
+    if (x < e0) return 0.0f;
+    if (x > e1) return 1.0f;
+    return (x - e0) / (e1 - e0);
+}
+static float gt_tonemap_(float x, float p, float a, float m, float l, float c, float b)  // tonemapping.rs:68-96
+{
+    if (x < 0.0f) return b;
+    const float l0 = (p - m) * l / a;
+    const float w0 = 1.0f - gt_smoothstep_(x, 0.0f, m);
+    const float w2 = gt_lerp_(x, m + l0, m + l0);
+    const float w1 = 1.0f - w0 - w2;
+    const float t = (m * std::pow(x / m, c) + b) * w0;                                   // gt_toe :5
+    const float u = (m + a * (x - m)) * w1;                                              // gt_linear :2
+    const float s0 = m + l0, s1 = m + a * l0, c2 = a * p / (p - s1);
+    const float v = (p - (p - s1) * std::exp(-c2 * (x - s0) / p)) * w2;                  // gt_shoulder :8-16
+    return t + u + v;
+}
+static uint8_t as_u8(float v) { return !(v > 0.0f) ? 0 : (v >= 255.0f ? 255 : (uint8_t)v); }  // Rust `as u8`
+void po_tonemap_rgb8(const float* accum_rgba, uint32_t W, uint32_t H, int flip_y, uint8_t* rgb)
+{
+    for (uint32_t y = 0; y < H; ++y)
+        for (uint32_t x = 0; x < W; ++x)
+        {
+            const float* a = accum_rgba + ((size_t)y * W + x) * 4;
+            uint8_t* o = rgb + ((size_t)(flip_y ? H - 1 - y : y) * W + x) * 3;
+            for (int k = 0; k < 3; ++k) o[k] = as_u8(std::pow(gt_tonemap_(a[k] / a[3], 1.0f, 1.0f, 0.22f, 0.4f, 1.33f, 0.0f), 1.0f / 2.2f) * 255.0f);
+        }
+}
+
 // ---- frame driver: main.rs:181-207 + accumulate.wgsl:20-23 ------------------------------------------------
 // accum[W*H*4] += (rgb, 1) per sample; position[W*H*4], id[W*H] as main.rs:204-206 (may be null).
 // counters[14] += extend, shadow, probe, paths, bounces, extend{boxes,tris,insts}, lights{boxes,tris,insts}, shadow{boxes,tris,insts}.

@@ -26,7 +26,7 @@ EXPORTS = [
     "ptb_set_build_threads", "ptb_bvh_blas_counts", "ptb_bvh_blas_nodes", "ptb_bvh_blas_triangles", "ptb_bvh_tlas_counts", "ptb_bvh_tlas_nodes",
     "ptb_light_count", "ptb_light_sampler", "ptb_bvh_stats", "ptb_trace_closest", "ptb_trace_any", "ptb_trace_upload", "ptb_trace_resident",
     "ptb_trace_download", "ptb_set_camera", "ptb_camera_rays", "ptb_ss_sobol", "ptb_rng_stream", "ptb_frame_begin", "ptb_render", "ptb_read_accum",
-    "ptb_read_aux", "ptb_enable_second_moment", "ptb_read_second_moment", "ptb_accum_device_ptr", "ptb_bind_accum", "ptb_get_counters",
+    "ptb_read_aux", "ptb_read_rgb8", "ptb_enable_second_moment", "ptb_read_second_moment", "ptb_accum_device_ptr", "ptb_bind_accum", "ptb_get_counters",
     "ptb_reset_counters", "ptb_set_profiling", "ptb_get_timing", "ptb_get_iteration_log", "ptb_set_option",
 ]
 
@@ -129,8 +129,11 @@ class Context:
         self._ck(self.L.ptb_scene_upload(self.h, _p(verts), C.c_uint64(verts.shape[0]), C.byref(bd), len(sd.blas), C.byref(inst), len(sd.instances)))
         self.sd = sd
         if build:
-            self._ck(self.L.ptb_set_build_threads(self.h, threads))
-            self._ck(self.L.ptb_build(self.h))
+            self.build(threads)
+
+    def build(self, threads=0):
+        self._ck(self.L.ptb_set_build_threads(self.h, threads))
+        self._ck(self.L.ptb_build(self.h))
 
     def set_env(self, rgb):
         rgb = np.ascontiguousarray(rgb, np.float32)
@@ -246,6 +249,12 @@ class Context:
         if out is None:
             out = np.zeros((self.height, self.width, 4), np.float32)
         self._ck(self.L.ptb_read_accum(self.h, _p(out)))
+        return out
+
+    def read_rgb8(self, flip_y=True):
+        """Tonemapped 8-bit image of the accumulation buffer (write_image, image_helper.rs:37-58), top row first by default."""
+        out = np.zeros((self.height, self.width, 3), np.uint8)
+        self._ck(self.L.ptb_read_rgb8(self.h, _p(out), int(flip_y)))
         return out
 
     def read_second_moment(self):

@@ -21,6 +21,7 @@
 #include "camera_host.h"
 #include "context.h"
 #include "persist.cuh"
+#include "render_state.h"
 #include "wavefront.h"
 
 namespace ptb {
@@ -489,6 +490,15 @@ __global__ void k_rng_stream(unsigned long long seed, uint32_t pixel, uint32_t s
     if (blockIdx.x || threadIdx.x) return;
     Rng r = rng_stream(seed, pixel, sample);
     for (uint32_t i = 0; i < n; ++i) out[i] = rng_u32(r);
+}
+
+bool render_state_frame(ptb_context* ctx, float4** accum, uint32_t* W, uint32_t* H)
+{
+    if (!ctx->rs || !ctx->rs->accum) return false;
+    *accum = ctx->rs->accum;
+    *W = ctx->rs->W;
+    *H = ctx->rs->H;
+    return true;
 }
 
 void render_state_destroy(ptb_context* ctx)

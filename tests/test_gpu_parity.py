@@ -215,3 +215,54 @@ def test_full_size_properties_c3(ptb, po, scenes):
     sc = po.OracleScene(sd)
     sl = slice(0, 1 << 15)
     compare_closest(sc.trace_closest(o[sl], d[sl], tm[sl]), {k: v[sl] for k, v in w.items()}, sc, o[sl], d[sl], tm[sl])
+
+
+def test_output_stage_rgb8(ptb, po, scenes, tmp_path):
+    """The step after the path: k_tonemap_rgb8 against the oracle's restatement of write_image
+    (image_helper.rs:37-58, tonemapping.rs:68-96) on the same accumulation buffer.  powf/expf are libm on the CPU and CUDA
+    device functions here, so a value sitting on an integer boundary may truncate differently: tolerance 1 LSB."""
+    from path_tracer_b200 import image_io
+    sd = scenes.scene_c2()
+    ctx = ptb.Context(0)
+    ctx.upload(sd)
+    W, H, N = 160, 90, 8
+    ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
+    ctx.frame_begin(W, H)
+    ctx.render(0, N, seed=7, max_bounces=sd.max_bounces)
+    acc = ctx.read_accum()
+    for flip in (True, False):
+        got, ref = ctx.read_rgb8(flip_y=flip).astype(np.int32), po.tonemap_rgb8(acc, flip_y=flip).astype(np.int32)
+        assert np.abs(got - ref).max() <= 1 and (got != ref).mean() < 0.01
+    img = ctx.read_rgb8()
+    assert img[: H // 8].mean() < img[H // 3: 2 * H // 3].mean()  # top rows: dark background above the box; middle: lit interior
+    p = tmp_path / "c2.png"
+    image_io.write_png(p, img)
+    assert np.array_equal((image_io.read_png(p) * 255.0 + 0.5).astype(np.uint8), img)
+
+
+def test_env_map_render_same_streams(ptb, po, scenes, tmp_path):
+    """Env-map ingest (image_helper.rs:25-33) feeding the miss branch (integrator.rs:254-262): the same PNG,
+    loaded with load_env, on both sides; equal RNG streams -> path-by-path agreement."""
+    from path_tracer_b200 import image_io
+    rng = np.random.default_rng(11)
+    png = (rng.random((16, 32, 3)) * 255).astype(np.uint8)
+    p = tmp_path / "env.png"
+    image_io.write_png(p, png)
+    env = image_io.load_env(p)
+    sd = scenes.scene_c2()
+    sc = po.OracleScene(sd)
+    sc.set_env(env)
+    ctx = ptb.Context(0)
+    ctx.upload(sd, build=False)
+    ctx.set_env(env)
+    ctx.build()
+    W, H, N = 128, 72, 4
+    ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
+    ctx.frame_begin(W, H)
+    ctx.render(0, N, seed=21, max_bounces=sd.max_bounces)
+    img = ctx.read_accum()
+    ref = sc.render(width=W, height=H, sample_count=N, seed=21)
+    A, B = ref["accum"][..., :3] / N, img[..., :3] / N
+    assert B[:4].mean() > 0.05  # the background is the env map now, not the constant 0.006
+    rel = np.abs(A - B).max(axis=2) / (np.abs(A).max(axis=2) + 1e-3)
+    assert (rel > 1e-3).mean() < 0.01
