@@ -84,7 +84,11 @@ struct Collapser
         if (is_tlas)
         {
             const HostTlasNode& n = ((const HostTlas*)tv.self)->nodes[bin_id];
-            h.count = 0;
+            // count = wide root of the instance's BLAS | TLAS_IDENTITY_FLAG when inv_matrix is bit-for-bit the identity with a +0
+            // translation: the traversal then needs no InstanceRow access to enter the instance
+            static const float ident[12] = {1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f};
+            const HostBlas& B = sc.blas[((const HostTlas*)tv.self)->blas_ids[n.a]];
+            h.count = B.wide_root | (std::memcmp(n.inv, ident, sizeof(ident)) == 0 ? TLAS_IDENTITY_FLAG : 0u);
             h.first = inst_base + n.b;
         }
         else

@@ -54,7 +54,8 @@ static_assert(sizeof(WideNode) == 80, "WideNode must be 80 bytes");
 // BLAS level: exact AABB of one reference leaf (LeafSingle: the primitive's own box, blas_bvh.rs:69-74; Leaf: the union,
 // :78), count = number of primitives (bit 31 set: the leaf is the BLAS root -> closest-hit uses t_estimate = 0 and no
 // box test, blas.rs:217), first = first triangle slot (planes at tri_planes[3*slot..], prim id at tri_prim[slot]).
-// TLAS level: exact AABB of the reference TLAS leaf (AABB::transform of the BLAS root box, tlas_bvh.rs:94), count unused,
+// TLAS level: exact AABB of the reference TLAS leaf (AABB::transform of the BLAS root box, tlas_bvh.rs:94), count = wide root
+// of the BLAS (bit 31: inv_matrix is exactly the identity),
 // first = instance ordinal (row of the instance table).
 struct LeafHeader
 {
@@ -65,6 +66,7 @@ struct LeafHeader
 };
 static_assert(sizeof(LeafHeader) == 32, "LeafHeader must be 32 bytes");
 constexpr uint32_t LEAF_ROOT_FLAG = 0x80000000u;
+constexpr uint32_t TLAS_IDENTITY_FLAG = 0x80000000u;  // TLAS-level header: count = BLAS wide root | this flag
 
 // ---- instance table row, 128 B ------------------------------------------------------------------------------------
 struct InstanceRow

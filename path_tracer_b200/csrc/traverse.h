@@ -73,6 +73,24 @@ PTB_HD void transform_ray(TravRay& out, V3 o, V3 d, const float* inv12)
 
 // Byte k of w as the float 2^23 + 256*byte: one byte-permute places the byte in mantissa bits 8..15 of 0x4B000000
 // (no integer-to-float conversion); the 2^23 bias and the factor 256 are folded into the plane equations below.
+// Ray::transform into an instance when the world ray's exact reciprocal is known: a component of the transformed direction
+// that is bit-identical to the world direction's (identity / translation-only instances, or an axis a rotation leaves
+// alone) reuses the world reciprocal instead of dividing again — same bits, since 1/x is a function of x's bits.
+PTB_HD void transform_ray_reuse(TravRay& out, V3 o, V3 d, V3 inv_d, const float* inv12)
+{
+    V3 c0 = ex::v3(inv12[0], inv12[1], inv12[2]), c1 = ex::v3(inv12[3], inv12[4], inv12[5]), c2 = ex::v3(inv12[6], inv12[7], inv12[8]);
+    V3 t = ex::v3(inv12[9], inv12[10], inv12[11]);
+    out.o = ex::add(ex::m3_mul(c0, c1, c2, o), t);
+    const V3 dd = ex::m3_mul(c0, c1, c2, d);
+    out.d = dd;
+    out.inv.x = ex::bits(dd.x) == ex::bits(d.x) ? inv_d.x : ex::rcp(dd.x);
+    out.inv.y = ex::bits(dd.y) == ex::bits(d.y) ? inv_d.y : ex::rcp(dd.y);
+    out.inv.z = ex::bits(dd.z) == ex::bits(d.z) ? inv_d.z : ex::rcp(dd.z);
+    out.idq = ex::v3(finite_recip_of(out.inv.x), finite_recip_of(out.inv.y), finite_recip_of(out.inv.z));
+    uint32_t oct = (dd.x < 0.0f ? 4u : 0u) | (dd.y < 0.0f ? 2u : 0u) | (dd.z < 0.0f ? 1u : 0u);
+    out.oi = 7u ^ oct;
+}
+
 PTB_HD float qbyte_biased(uint32_t w, int k)
 {
 #if defined(__CUDA_ARCH__)
@@ -259,12 +277,19 @@ PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, uint2* stack)
                 if (ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), s.ray.o, s.ray.inv, s.t_max, &t_enter))
                 {
                     s.cur_inst = ex::bits(h1.w);
-                    const float4* ip = (const float4*)S.inst[s.cur_inst].inv;
-                    const float4 i0 = PTB_LDG4F(ip), i1 = PTB_LDG4F(ip + 1), i2 = PTB_LDG4F(ip + 2);
-                    const float inv12[12] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w, i2.x, i2.y, i2.z, i2.w};
-                    transform_ray(s.ray, s.ow, s.dw, inv12);
+                    const uint32_t cw = ex::bits(h0.w);
+                    float inv12[12] = {1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f};
+                    if (!(cw & TLAS_IDENTITY_FLAG))
+                    {
+                        const float4* ip = (const float4*)S.inst[s.cur_inst].inv;
+                        const float4 i0 = PTB_LDG4F(ip), i1 = PTB_LDG4F(ip + 1), i2 = PTB_LDG4F(ip + 2);
+                        inv12[0] = i0.x; inv12[1] = i0.y; inv12[2] = i0.z; inv12[3] = i0.w; inv12[4] = i1.x; inv12[5] = i1.y;
+                        inv12[6] = i1.z; inv12[7] = i1.w; inv12[8] = i2.x; inv12[9] = i2.y; inv12[10] = i2.z; inv12[11] = i2.w;
+                    }
+                    // the arithmetic of Ray::transform is carried out even for the identity (x*1 + y*0 + ... decides the sign of zeros)
+                    transform_ray_reuse(s.ray, s.ow, s.dw, s.invw, inv12);
                     s.blas_sp = s.sp;
-                    s.node = PTB_LDGU(&S.inst[s.cur_inst].wide_root);
+                    s.node = cw & ~TLAS_IDENTITY_FLAG;
                 }
             }
             else s.G = e;
