@@ -1,6 +1,7 @@
 // kernels_trace.cu — fixed-batch TLAS::intersect / TLAS::any_intersect kernels (ptb_trace_*).
-// Persistent threads: the grid is a multiple of the SM count and every warp pulls batches of 32 rays from a global
-// counter until the batch is exhausted (one atomic per warp-batch).  The per-ray work is traverse.h.
+// 8-wide layout: the dynamic-fetch persistent loop of persist.cuh (a warp keeps 32 rays in flight, lanes whose ray has
+// finished write their result and take the next ray from a global cursor, 64 rays per atomic).  Reference-order binary
+// layout (kernel = 1, the checker for traversal order): one ray per thread, grid-stride.  The per-ray work is traverse.h.
 #include "context.h"
 #include "persist.cuh"
 
