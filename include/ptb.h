@@ -156,6 +156,34 @@ int ptb_read_aux(ptb_context* ctx, float* position4, uint32_t* id);
  * constants of ImageHelper::write_image (image_helper.rs:44; tonemapping.rs:68-96), gamma 1/2.2, * 255 `as u8`.  rgb: W*H*3 bytes.
  * flip_y != 0 writes the top image row first (the accumulation buffer has row 0 at the bottom, camera.rs:96). */
 int ptb_read_rgb8(ptb_context* ctx, uint8_t* rgb, int flip_y);
+/* ---- temporal accumulation for a moving camera: State::update (state.rs:505-579) as CUDA kernels --------------------------
+ * The reference keeps an accumulation texture inside `State` and, after every frame, dispatches either accumulate.wgsl
+ * (camera unchanged: accumulation += (rgb, 1)) or velocity.wgsl + compute.wgsl (camera moved: reproject last frame through
+ * `last_inv_projection`, validate by model id, Catmull-Rom history fetch, variance clip in YCoCg, blend 15 % of the new frame),
+ * then copies the output into the accumulation texture.  Here the accumulation texture is a device buffer owned by the context.
+ *   ptb_state_update           = State::update with its own argument list: host slices `data` (rgb, 1), `position` (xyz, t),
+ *                                `id` ((previous << 16) | current, main.rs:206), W*H elements each, row 0 at the bottom.
+ *   ptb_state_update_resident  = the same on the context's current frame buffers (no host round trip): the accumulation
+ *                                buffer of ptb_frame_begin/ptb_render is the frame input (read as sum / count), position and
+ *                                id are the aux buffers.  Per displayed frame: ptb_frame_next, ptb_render(1 sample), this call.
+ *   `inv_projection` / `last_inv_projection` are what the reference passes under those names: (cam.matrix *
+ *   cam.inv_projection).inverse() of this and of the previous frame (main.rs:209-216), column-major;
+ *   ptb_camera_view_projection returns it for the camera set by ptb_set_camera.
+ *   ptb_state_reset            = a new State (zeroed textures) of the given size.
+ *   ptb_state_read             = accumulation texture (rgba, W*H*4 floats; display value = rgb / w, shader.wgsl:63) and, optionally,
+ *                                the velocity texture written by the last moving-camera update (W*H*2 floats).
+ *   ptb_frame_next             = start the next frame of the same size keeping the id history (ptb_frame_begin clears it). */
+int ptb_state_reset(ptb_context* ctx, uint32_t width, uint32_t height);
+int ptb_state_update(ptb_context* ctx, uint32_t width, uint32_t height, const float* data, const float* position, const uint32_t* id,
+                     const float inv_projection[16], const float last_inv_projection[16]);
+int ptb_state_update_resident(ptb_context* ctx, const float inv_projection[16], const float last_inv_projection[16]);
+int ptb_state_read(ptb_context* ctx, float* rgba, float* velocity2);
+int ptb_state_read_rgb8(ptb_context* ctx, uint8_t* rgb, int flip_y);   /* ptb_read_rgb8 of the accumulation texture */
+int ptb_state_device_ptr(ptb_context* ctx, void** dptr, size_t* bytes);
+/* device time (CUDA events) and count of the update kernels launched while ptb_set_profiling was on */
+int ptb_state_timing(ptb_context* ctx, float* ms_total, uint32_t* launches, int reset);
+int ptb_frame_next(ptb_context* ctx);
+int ptb_camera_view_projection(ptb_context* ctx, float m16[16]);
 /* Optional second moment (sum of squared sample values) for statistical parity tests; must be enabled before ptb_frame_begin. */
 int ptb_enable_second_moment(ptb_context* ctx, int enable);
 int ptb_read_second_moment(ptb_context* ctx, float* rgba);

@@ -253,3 +253,31 @@ def tonemap_rgb8(accum, flip_y=True):
     out = np.zeros((H, W, 3), np.uint8)
     lib().po_tonemap_rgb8(_p(accum), W, H, int(flip_y), _p(out))
     return out
+
+
+def state_update(data, position, ids, inv_projection, last_inv_projection, accumulation):
+    """State::update (state.rs:505-579) on host arrays.  data/position/accumulation [H,W,4] f32, ids [H,W] u32, matrices 16 floats
+    column-major.  Returns (new accumulation, velocity [H,W,2], taa_ran)."""
+    data = np.ascontiguousarray(data, np.float32)
+    position = np.ascontiguousarray(position, np.float32)
+    ids = np.ascontiguousarray(ids, np.uint32)
+    acc = np.array(accumulation, np.float32, order="C", copy=True)
+    H, W = data.shape[:2]
+    vel = np.zeros((H, W, 2), np.float32)
+    a = np.ascontiguousarray(np.asarray(inv_projection, np.float32).reshape(16))
+    b = np.ascontiguousarray(np.asarray(last_inv_projection, np.float32).reshape(16))
+    f = lib().po_state_update
+    f.restype = C.c_int
+    ran = f(C.c_uint32(W), C.c_uint32(H), _p(data), _p(position), _p(ids), _p(a), _p(b), _p(acc), _p(vel))
+    return acc, vel, bool(ran)
+
+
+def view_projection(origin, target, fov_deg, aspect):
+    """World -> clip matrix the reference passes as `inv_projection` (main.rs:209-216), float64, column-major [16]."""
+    o = np.ascontiguousarray(origin, np.float32)
+    t = np.ascontiguousarray(target, np.float32)
+    m = np.zeros(16, np.float64)
+    f = lib().po_view_projection
+    f.restype = None
+    f(_p(o), _p(t), C.c_float(fov_deg), C.c_float(aspect), _p(m))
+    return m

@@ -9,6 +9,7 @@
 #include <thread>
 
 #include "po_shading.hpp"
+#include "po_temporal.hpp"
 
 using namespace po;
 
@@ -444,6 +445,39 @@ void po_tonemap_rgb8(const float* accum_rgba, uint32_t W, uint32_t H, int flip_y
             const float* a = accum_rgba + ((size_t)y * W + x) * 4;
             uint8_t* o = rgb + ((size_t)(flip_y ? H - 1 - y : y) * W + x) * 3;
             for (int k = 0; k < 3; ++k) o[k] = as_u8(std::pow(gt_tonemap_(a[k] / a[3], 1.0f, 1.0f, 0.22f, 0.4f, 1.33f, 0.0f), 1.0f / 2.2f) * 255.0f);
+        }
+}
+
+// ---- State::update (state.rs:505-579): accumulate.wgsl / velocity.wgsl + compute.wgsl on host arrays -------------
+// accumulation[W*H*4] in/out, velocity[W*H*2] out (moving camera only).  Returns 1 when the TAA path ran.
+int po_state_update(uint32_t W, uint32_t H, const float* data, const float* position, const uint32_t* id, const float* inv_projection, const float* last_inv_projection,
+                    float* accumulation, float* velocity)
+{
+    return state_update((int)W, (int)H, data, position, id, inv_projection, last_inv_projection, accumulation, velocity);
+}
+// (cam.matrix * cam.inv_projection).inverse() (main.rs:209-216) for Camera::new(origin, target, fov, aspect): evaluated in
+// double precision (exact view-projection rounded once), used by tests to bound the f32 cofactor inverse of the product path.
+void po_view_projection(const float* origin, const float* target, float fov_deg, float aspect, double* m16)
+{
+    double e[3] = {origin[0], origin[1], origin[2]}, f[3] = {target[0] - e[0], target[1] - e[1], target[2] - e[2]};
+    double fl = std::sqrt(f[0] * f[0] + f[1] * f[1] + f[2] * f[2]);
+    for (double& v : f) v /= fl;
+    double s[3] = {f[1] * 0.0 - f[2] * 1.0, f[2] * 0.0 - f[0] * 0.0, f[0] * 1.0 - f[1] * 0.0};  // f x (0,1,0)
+    double sl = std::sqrt(s[0] * s[0] + s[1] * s[1] + s[2] * s[2]);
+    for (double& v : s) v /= sl;
+    double u[3] = {s[1] * f[2] - s[2] * f[1], s[2] * f[0] - s[0] * f[2], s[0] * f[1] - s[1] * f[0]};
+    // view (look_at_rh), column-major
+    double V[16] = {s[0], u[0], -f[0], 0, s[1], u[1], -f[1], 0, s[2], u[2], -f[2], 0, -(s[0] * e[0] + s[1] * e[1] + s[2] * e[2]), -(u[0] * e[0] + u[1] * e[1] + u[2] * e[2]),
+                    (f[0] * e[0] + f[1] * e[1] + f[2] * e[2]), 1};
+    // perspective_infinite_rh(fov, aspect, z_near = 1): cols (g/aspect,0,0,0) (0,g,0,0) (0,0,-1,-1) (0,0,-z_near,0)
+    double g = 1.0 / std::tan(0.5 * (double)fov_deg * 3.14159265358979323846 / 180.0);
+    double P[16] = {g / aspect, 0, 0, 0, 0, g, 0, 0, 0, 0, -1, -1, 0, 0, -1, 0};
+    for (int c = 0; c < 4; ++c)
+        for (int r = 0; r < 4; ++r)
+        {
+            double a = 0;
+            for (int k = 0; k < 4; ++k) a += P[k * 4 + r] * V[c * 4 + k];
+            m16[c * 4 + r] = a;
         }
 }
 

@@ -28,6 +28,8 @@ EXPORTS = [
     "ptb_trace_download", "ptb_set_camera", "ptb_camera_rays", "ptb_ss_sobol", "ptb_rng_stream", "ptb_frame_begin", "ptb_render", "ptb_read_accum",
     "ptb_read_aux", "ptb_read_rgb8", "ptb_enable_second_moment", "ptb_read_second_moment", "ptb_accum_device_ptr", "ptb_bind_accum", "ptb_get_counters",
     "ptb_reset_counters", "ptb_set_profiling", "ptb_get_timing", "ptb_get_iteration_log", "ptb_set_option",
+    "ptb_state_reset", "ptb_state_update", "ptb_state_update_resident", "ptb_state_read", "ptb_state_read_rgb8", "ptb_state_device_ptr", "ptb_state_timing", "ptb_frame_next",
+    "ptb_camera_view_projection",
 ]
 
 
@@ -255,6 +257,59 @@ class Context:
         """Tonemapped 8-bit image of the accumulation buffer (write_image, image_helper.rs:37-58), top row first by default."""
         out = np.zeros((self.height, self.width, 3), np.uint8)
         self._ck(self.L.ptb_read_rgb8(self.h, _p(out), int(flip_y)))
+        return out
+
+    # ---- temporal accumulation: State::update (state.rs:505-579) ----------------------------------------------------
+    def frame_next(self):
+        """Next frame of the same size: clears the frame input, keeps the id history (main.rs:204-206)."""
+        self._ck(self.L.ptb_frame_next(self.h))
+
+    def view_projection(self):
+        """(cam.matrix * cam.inv_projection).inverse() (main.rs:209-216) of the current camera, column-major [16]."""
+        m = np.zeros(16, np.float32)
+        self._ck(self.L.ptb_camera_view_projection(self.h, _p(m)))
+        return m
+
+    def state_reset(self, width, height):
+        self._ck(self.L.ptb_state_reset(self.h, C.c_uint32(width), C.c_uint32(height)))
+
+    def state_update(self, data, position, ids, inv_projection, last_inv_projection):
+        """State::update with the reference's argument list (host arrays [H,W,4], [H,W,4], [H,W] u32, two Mat4)."""
+        data = np.ascontiguousarray(data, np.float32)
+        position = np.ascontiguousarray(position, np.float32)
+        ids = np.ascontiguousarray(ids, np.uint32)
+        H, W = data.shape[:2]
+        if position.shape[:2] != (H, W) or ids.shape[:2] != (H, W):
+            raise ValueError("data, position and id must have the same image size")
+        a = np.ascontiguousarray(np.asarray(inv_projection, np.float32).reshape(16))
+        b = np.ascontiguousarray(np.asarray(last_inv_projection, np.float32).reshape(16))
+        self._ck(self.L.ptb_state_update(self.h, C.c_uint32(W), C.c_uint32(H), _p(data), _p(position), _p(ids), _p(a), _p(b)))
+        self._state_shape = (H, W)
+
+    def state_update_resident(self, inv_projection, last_inv_projection):
+        """The same on the context's own frame buffers (accumulation buffer as frame input, aux position / id)."""
+        a = np.ascontiguousarray(np.asarray(inv_projection, np.float32).reshape(16))
+        b = np.ascontiguousarray(np.asarray(last_inv_projection, np.float32).reshape(16))
+        self._ck(self.L.ptb_state_update_resident(self.h, _p(a), _p(b)))
+        self._state_shape = (self.height, self.width)
+
+    def state_read(self, velocity=False):
+        H, W = self._state_shape
+        out = np.zeros((H, W, 4), np.float32)
+        vel = np.zeros((H, W, 2), np.float32) if velocity else None
+        self._ck(self.L.ptb_state_read(self.h, _p(out), _p(vel)))
+        return (out, vel) if velocity else out
+
+    def state_timing(self, reset=True):
+        """(total ms, launches) of the update kernels timed while set_profiling(True)"""
+        ms, n = C.c_float(), C.c_uint32()
+        self._ck(self.L.ptb_state_timing(self.h, C.byref(ms), C.byref(n), int(reset)))
+        return ms.value, n.value
+
+    def state_read_rgb8(self, flip_y=True):
+        H, W = self._state_shape
+        out = np.zeros((H, W, 3), np.uint8)
+        self._ck(self.L.ptb_state_read_rgb8(self.h, _p(out), int(flip_y)))
         return out
 
     def read_second_moment(self):

@@ -36,6 +36,8 @@ struct DBuf  // owning device array
 // SoA wavefront state of the renderer (render.cu); one slot per pixel (path regeneration keeps a slot on its pixel, so
 // per-pixel accumulation needs no atomics).
 struct RenderState;
+// accumulation texture + velocity of the temporal pass (temporal.cu)
+struct TemporalState;
 
 }  // namespace ptb
 
@@ -89,6 +91,7 @@ struct ptb_context
     int second_moment = 0;
 
     ptb::RenderState* rs = nullptr;
+    ptb::TemporalState* ts = nullptr;
 
     int fail(int code, const std::string& m)
     {
@@ -112,6 +115,7 @@ struct ptb_context
 namespace ptb {
 // render.cu
 void render_state_destroy(ptb_context* ctx);
+void temporal_state_destroy(ptb_context* ctx);
 // trace kernels (kernels_trace.cu)
 struct TraceArgs
 {

@@ -62,6 +62,19 @@ __global__ void __launch_bounds__(256) k_tonemap_rgb8(const float4* accum, uint3
 
 using namespace ptb;
 
+static int read_rgb8(ptb_context* ctx, const float4* src, uint32_t W, uint32_t H, uint8_t* rgb, int flip_y)
+{
+    PTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    DBuf<unsigned char> d;
+    PTB_CUDA(ctx, d.resize((size_t)W * H * 3));
+    k_tonemap_rgb8<<<(W * H + 255) / 256, 256, 0, ctx->stream>>>(src, W, H, flip_y, d.p);
+    PTB_CUDA(ctx, cudaGetLastError());
+    PTB_CUDA(ctx, cudaMemcpyAsync(rgb, d.p, (size_t)W * H * 3, cudaMemcpyDeviceToHost, ctx->stream));
+    PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    d.release();
+    return PTB_OK;
+}
+
 extern "C" int ptb_read_rgb8(ptb_context* ctx, uint8_t* rgb, int flip_y)
 {
     if (!ctx) return PTB_ERR_INVALID;
@@ -69,13 +82,15 @@ extern "C" int ptb_read_rgb8(ptb_context* ctx, uint8_t* rgb, int flip_y)
     float4* accum = nullptr;
     uint32_t W = 0, H = 0;
     if (!render_state_frame(ctx, &accum, &W, &H) || !rgb) return ctx->fail(PTB_ERR_INVALID, "no frame");
-    PTB_CUDA(ctx, cudaSetDevice(ctx->device));
-    DBuf<unsigned char> d;
-    PTB_CUDA(ctx, d.resize((size_t)W * H * 3));
-    k_tonemap_rgb8<<<(W * H + 255) / 256, 256, 0, ctx->stream>>>(accum, W, H, flip_y, d.p);
-    PTB_CUDA(ctx, cudaGetLastError());
-    PTB_CUDA(ctx, cudaMemcpyAsync(rgb, d.p, (size_t)W * H * 3, cudaMemcpyDeviceToHost, ctx->stream));
-    PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    d.release();
-    return PTB_OK;
+    return read_rgb8(ctx, accum, W, H, rgb, flip_y);
+}
+
+extern "C" int ptb_state_read_rgb8(ptb_context* ctx, uint8_t* rgb, int flip_y)
+{
+    if (!ctx) return PTB_ERR_INVALID;
+    if (ctx->host_only) return ctx->fail(PTB_ERR_NO_DEVICE, "host-only context: no CUDA device bound (no CPU fallback)");
+    const float4* hist = nullptr;
+    uint32_t W = 0, H = 0;
+    if (!temporal_state_image(ctx, &hist, &W, &H) || !rgb) return ctx->fail(PTB_ERR_INVALID, "no temporal state");
+    return read_rgb8(ctx, hist, W, H, rgb, flip_y);
 }

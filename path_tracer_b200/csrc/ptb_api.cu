@@ -81,6 +81,7 @@ void ptb_destroy(ptb_context* ctx)
         cudaSetDevice(ctx->device);
         cudaStreamSynchronize(ctx->stream);
         render_state_destroy(ctx);
+        temporal_state_destroy(ctx);
         free_device(ctx);
         cudaStreamDestroy(ctx->stream);
     }

@@ -501,6 +501,14 @@ bool render_state_frame(ptb_context* ctx, float4** accum, uint32_t* W, uint32_t*
     return true;
 }
 
+bool render_state_aux(ptb_context* ctx, float4** position, uint32_t** id)
+{
+    if (!ctx->rs || !ctx->rs->position.p || !ctx->rs->id.p) return false;
+    *position = ctx->rs->position.p;
+    *id = ctx->rs->id.p;
+    return true;
+}
+
 void render_state_destroy(ptb_context* ctx)
 {
     RenderState* rs = ctx->rs;
@@ -635,6 +643,26 @@ int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height)
     PTB_CUDA(ctx, cudaMemsetAsync(rs.position.p, 0, (size_t)npix * 16, ctx->stream));
     PTB_CUDA(ctx, cudaMemsetAsync(rs.id.p, 0, (size_t)npix * 4, ctx->stream));
     if (fresh) PTB_CUDA(ctx, cudaMemsetAsync(rs.counters.p, 0, sizeof(WfCounters), ctx->stream));  // statistics persist until ptb_reset_counters
+    return PTB_OK;
+}
+
+int ptb_frame_next(ptb_context* ctx)
+{
+    REQUIRE_DEVICE(ctx);
+    if (!ctx->rs || !ctx->rs->accum) return ctx->fail(PTB_ERR_INVALID, "call ptb_frame_begin first");
+    RenderState& rs = *ctx->rs;
+    PTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    // the reference overwrites `data` and `position` every frame and shifts `id` (main.rs:204-206): only the id history survives
+    PTB_CUDA(ctx, cudaMemsetAsync(rs.accum, 0, (size_t)rs.npix * 16, ctx->stream));
+    if (ctx->second_moment) PTB_CUDA(ctx, cudaMemsetAsync(rs.accum_sq.p, 0, (size_t)rs.npix * 16, ctx->stream));
+    return PTB_OK;
+}
+
+int ptb_camera_view_projection(ptb_context* ctx, float m16[16])
+{
+    if (!ctx) return PTB_ERR_INVALID;
+    if (!ctx->cam_set || !m16) return ctx->fail(PTB_ERR_INVALID, "camera not set");
+    mat4_inverse(ctx->cam_m, m16);  // (cam.matrix * cam.inv_projection).inverse(), main.rs:209-216
     return PTB_OK;
 }
 

@@ -24,6 +24,14 @@ def bits(a):
     return np.ascontiguousarray(a, np.float32).view(np.uint32)
 
 
+def same_bits_or_nan(a, b):
+    """float32 arrays equal bit for bit, except that any NaN matches any NaN (sign and payload of a NaN depend on operand order and
+    on the machine: x86 returns the first NaN operand or the negative default NaN, the GPU the canonical 0x7fffffff)."""
+    a = np.ascontiguousarray(a, np.float32)
+    b = np.ascontiguousarray(b, np.float32)
+    return a.shape == b.shape and bool(np.all((bits(a) == bits(b)) | (np.isnan(a) & np.isnan(b))))
+
+
 TIE_ULPS = 4
 
 

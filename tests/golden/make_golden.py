@@ -27,4 +27,23 @@ np.savez_compressed(os.path.join(HERE, "build_c2.npz"), meta=d0["meta"], boxes_b
                     tlas_boxes_bits=sc.tlas_dump(0)["boxes"].view(np.uint32))
 im = sc.render(width=64, height=36, sample_count=4, seed=5)
 np.savez_compressed(os.path.join(HERE, "render_c2_64x36_4spp_seed5.npz"), accum=im["accum"], id=im["id"])
+# State::update sequence (5 frames: static, moved, moved, static, moved) on seeded inputs: accumulation texture bits after every frame
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import temporal_inputs  # noqa: E402
+
+
+class _OracleState:
+    def __init__(self, W, H):
+        self.acc = np.zeros((H, W, 4), np.float32)
+        self.vel = np.zeros((H, W, 2), np.float32)
+
+    def update(self, data, pos, ids, inv, last):
+        self.acc, vel, ran = po.state_update(data, pos, ids, inv, last, self.acc)
+        if ran:
+            self.vel = vel
+
+
+stt = _OracleState(48, 27)
+seq = temporal_inputs.run_sequence(stt.update, lambda: stt.acc.copy(), po, 48, 27, 5, seed=11)
+np.savez_compressed(os.path.join(HERE, "temporal_48x27_seed11.npz"), acc_bits=np.stack(seq).view(np.uint32), vel_bits=stt.vel.view(np.uint32))
 print("golden vectors written")

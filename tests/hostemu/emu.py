@@ -99,3 +99,19 @@ def render(es, sd, width, height, sample_begin=0, sample_count=1, seed=1, max_bo
     mb = sd.max_bounces if max_bounces is None else max_bounces
     lib().emu_render(C.c_void_p(es.h), _p(m), _p(eye), width, height, sample_begin, sample_count, C.c_uint64(seed), mb, int(enable_nee), extend_kernel, _p(accum), _p(pos), _p(ids), _p(cnt))
     return dict(accum=accum, position=pos, id=ids, counters=dict(extend=int(cnt[0]), shadow=int(cnt[1]), probe=int(cnt[2]), paths=int(cnt[3]), iters=int(cnt[4])))
+
+
+def state_update(data, position, ids, inv_projection, last_inv_projection, history):
+    """temporal.cuh bodies on the host; returns (new accumulation, velocity or None)"""
+    data = np.ascontiguousarray(data, np.float32)
+    position = np.ascontiguousarray(position, np.float32)
+    ids = np.ascontiguousarray(ids, np.uint32)
+    history = np.ascontiguousarray(history, np.float32)
+    H, W = data.shape[:2]
+    a = np.asarray(inv_projection, np.float32).reshape(16)
+    b = np.ascontiguousarray(np.asarray(last_inv_projection, np.float32).reshape(16))
+    moved = not bool(np.all(a == b))
+    out = np.zeros((H, W, 4), np.float32)
+    vel = np.zeros((H, W, 2), np.float32)
+    lib().emu_state_update(W, H, _p(data), _p(position), _p(ids), _p(b), int(moved), _p(history), _p(out), _p(vel))
+    return out, (vel if moved else None)

@@ -11,6 +11,7 @@
 #include "../../path_tracer_b200/csrc/camera_host.h"
 #include "../../path_tracer_b200/csrc/host_scene.h"
 #include "../../path_tracer_b200/csrc/traverse.h"
+#include "../../path_tracer_b200/csrc/temporal.cuh"
 #include "../../path_tracer_b200/csrc/wavefront.h"
 
 using namespace ptb;
@@ -184,6 +185,27 @@ void emu_camera_rays(const float* cam_m16, const float* cam_eye3, uint64_t n, co
         o3[i * 3] = o.x; o3[i * 3 + 1] = o.y; o3[i * 3 + 2] = o.z;
         d3[i * 3] = d.x; d3[i * 3 + 1] = d.y; d3[i * 3 + 2] = d.z;
     }
+}
+// the per-texel bodies of k_resolve / k_accumulate (temporal.cuh) looped over the image; history in, out separate
+void emu_state_update(int W, int H, const float* data, const float* position, const uint32_t* id, const float* last16, int moved, const float* history, float* out, float* velocity)
+{
+    const tp::Image in{reinterpret_cast<const tp::F4*>(data), W, H, 0}, hist{reinterpret_cast<const tp::F4*>(history), W, H, 0};
+    const tp::Image pos{reinterpret_cast<const tp::F4*>(position), W, H, 0};
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x)
+        {
+            const size_t i = (size_t)y * W + x;
+            if (!moved)
+            {
+                for (int k = 0; k < 3; ++k) out[i * 4 + k] = history[i * 4 + k] + data[i * 4 + k];
+                out[i * 4 + 3] = history[i * 4 + 3] + 1.0f;
+                continue;
+            }
+            const tp::F2 v = tp::velocity_at(pos, last16, tp::F2{(float)W, (float)H}, x, y);
+            const tp::F4 r = tp::resolve_at(in, hist, pos, id, last16, x, y);
+            velocity[i * 2] = v.x; velocity[i * 2 + 1] = v.y;
+            out[i * 4] = r.x; out[i * 4 + 1] = r.y; out[i * 4 + 2] = r.z; out[i * 4 + 3] = r.w;
+        }
 }
 void emu_camera(const float* origin, const float* target, float fov_deg, float aspect, float* m16, float* eye3) { camera_setup(origin, target, fov_deg, aspect, m16, eye3); }
 }
