@@ -38,25 +38,25 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, ui
             const bool again = job.finish(tr, state == 2);
             if (state == 2) state = again ? 1 : 0;
         }
-        if (wbase < wend || global_more)
+        // deal work to the idle lanes; an item may need no traversal (start() false), so repeat while lanes stay idle and items remain
+        for (int pass = 0; pass < 4 && (wbase < wend || global_more); ++pass)
         {
             const unsigned idle = __ballot_sync(FULL, state == 0);
-            if (idle)
+            if (!idle) break;
+            if (wbase >= wend)
             {
-                if (wbase >= wend)
-                {
-                    const uint32_t want = (total - seen > fine_below) ? BATCH : (uint32_t)__popc(idle);
-                    uint32_t base = 0;
-                    if (lane == 0u) base = atomicAdd(cursor, want);
-                    base = __shfl_sync(FULL, base, 0);
-                    if (base >= total) { global_more = false; wbase = wend = 0u; }
-                    else { wbase = base; wend = min(base + want, total); seen = wend; if (wend == total) global_more = false; }
-                }
-                const uint32_t avail = wend - wbase, n = (uint32_t)__popc(idle);
-                const uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
-                if (state == 0 && rank < avail && job.start(wbase + rank, tr)) state = 1;
-                wbase += min(n, avail);
+                const uint32_t want = (total - seen > fine_below) ? BATCH : (uint32_t)__popc(idle);
+                uint32_t base = 0;
+                if (lane == 0u) base = atomicAdd(cursor, want);
+                base = __shfl_sync(FULL, base, 0);
+                if (base >= total) { global_more = false; wbase = wend = 0u; break; }
+                wbase = base; wend = min(base + want, total); seen = wend;
+                if (wend == total) global_more = false;
             }
+            const uint32_t avail = wend - wbase, n = (uint32_t)__popc(idle);
+            const uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
+            if (state == 0 && rank < avail && job.start(wbase + rank, tr)) state = 1;
+            wbase += min(n, avail);
         }
         const bool more = wbase < wend || global_more;
         unsigned busy = __ballot_sync(FULL, state == 1);

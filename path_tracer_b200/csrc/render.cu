@@ -29,7 +29,7 @@ namespace ptb {
 struct WfSet  // 64 B
 {
     uint32_t n_cont, n_term;  // consumed by k_extend (polled by the host: keep first)
-    uint32_t n_nee, pad0;
+    uint32_t n_nee, n_grp;    // n_grp: slot-ordered mode, live 32-slot groups listed for this iteration (polled with the two above)
     uint32_t n_mat[8];
     uint32_t cur_extend, cur_shade, cur_nee, pad;
 };
@@ -45,6 +45,8 @@ struct Queues
     uint32_t* term[2];  // slots whose path ended (to be finalised / regenerated)
     uint32_t* mat;      // 7 queues of npix entries each
     uint32_t* nee;      // slot | NEE_SHADOW_BIT | NEE_PROBE_BIT
+    uint32_t* grp[2];   // slot-ordered mode: ascending list of the 32-slot groups that still hold a live slot, double-buffered like cont/term
+    uint32_t* state;    // slot-ordered mode: per-slot WF_* flags of the last shade (WF_NEXT / WF_TERM / 0 = no samples left, | WF_SHADOW | WF_PROBE)
     uint32_t npix;
     WfCounters* c;
 };
@@ -63,11 +65,11 @@ struct RenderState
     DBuf<HitRec> hit;
     DBuf<ShadowRec> shadow;
     DBuf<ProbeRec> probe;
-    DBuf<uint32_t> id, q_cont0, q_cont1, q_term0, q_term1, q_mat, q_nee;
+    DBuf<uint32_t> id, q_cont0, q_cont1, q_term0, q_term1, q_mat, q_nee, slot_state, q_grp0, q_grp1;
     DBuf<unsigned long long> volset;
     DBuf<WfCounters> counters;
     float4* accum = nullptr;  // bound or own
-    uint32_t* h_flags = nullptr;  // pinned, POLL_RING x 2
+    uint32_t* h_flags = nullptr;  // pinned, POLL_RING x 4 (n_cont, n_term, n_nee, n_grp of every iteration)
     uint32_t log_iters = 0;       // iterations recorded in h_flags by the last ptb_render
     std::vector<cudaEvent_t> poll_events;
     std::vector<cudaEvent_t> prof_events;
@@ -81,6 +83,7 @@ struct RenderState
 };
 
 // ---- device helpers ------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void warp_push(uint32_t* q, uint32_t* counter, bool pred, uint32_t value)
 {
     const unsigned m = __ballot_sync(0xffffffffu, pred);
@@ -122,10 +125,13 @@ __global__ void __launch_bounds__(128) k_init(RenderView V, Queues Q, const uint
     if (V.accum_sq) V.accum_sq[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     V.id[i] = V.K == 1u ? id_px[i] : 0u;  // one slot per pixel: the slot continues the pixel's id history (main.rs:206)
     Q.term[0][i] = i;
+    Q.state[i] = WF_TERM;
+    if ((i & 31u) == 0u) Q.grp[0][i >> 5] = i >> 5;
     if (i == 0)
     {
         for (int s = 0; s < 3; ++s) Q.c->set[s] = WfSet{};
         Q.c->set[0].n_term = Q.npix;
+        Q.c->set[0].n_grp = (Q.npix + 31u) >> 5;
     }
 }
 
@@ -331,11 +337,10 @@ struct NeeJob
         stage = 1;
         ++n_probe;
     }
-    __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
+    __device__ __forceinline__ bool begin_slot(uint32_t slot_, uint32_t flags_, WideTrav& tr)
     {
-        const uint32_t e = Q.nee[idx];
-        slot = e & NEE_SLOT_MASK;
-        flags = ((e & NEE_SHADOW_BIT) ? WF_SHADOW : 0u) | ((e & NEE_PROBE_BIT) ? WF_PROBE : 0u);
+        slot = slot_;
+        flags = flags_;
         const float4 o4 = V.ray[slot].o;
         o = ex::v3(o4.x, o4.y, o4.z);
         r = V.path[slot].radiance;
@@ -348,6 +353,11 @@ struct NeeJob
         }
         else begin_probe(tr);
         return true;
+    }
+    __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
+    {
+        const uint32_t e = Q.nee[idx];
+        return begin_slot(e & NEE_SLOT_MASK, ((e & NEE_SHADOW_BIT) ? WF_SHADOW : 0u) | ((e & NEE_PROBE_BIT) ? WF_PROBE : 0u), tr);
     }
     __device__ __forceinline__ bool finish(WideTrav& tr, bool mine)
     {
@@ -417,6 +427,214 @@ __global__ void __launch_bounds__(128) k_nee_bin(RenderView V, Queues Q, uint32_
             if (mp) atomicAdd(&Q.c->stat_probe, (unsigned long long)__popc(mp));
             if (mt) atomicAdd(&Q.c->stat_probe_shadow, (unsigned long long)__popc(mt));
         }
+    }
+}
+
+// ---- slot-ordered ("dense") wavefront --------------------------------------------------------------------------------------
+// While most slots carry a live path (path regeneration keeps them busy until their samples run out) the queues buy nothing:
+// every slot has exactly one ray per iteration.  These kernels walk the slots in index order instead and keep a per-slot flag
+// word (Q.state = the WF_* flags of the slot's last shade):  no queue pushes, no atomics on the dependency chain, and all
+// per-slot records are read and written in address order (consecutive lanes = consecutive 32-byte records).  The unit of work
+// is a GROUP of 32 consecutive slots; k_shade_dense keeps an ascending list of the groups that still hold a live slot, so regions
+// of the image whose samples are exhausted (background pixels finish their samples long before the others) cost nothing.  The
+// host watches live slots / (32 x listed groups) and continues with the queue kernels (k_compact, then k_extend ... k_tail) once
+// the live slots are scattered thinly over the groups.
+struct DenseExtendJob
+{
+    const RenderView& V;
+    const Queues& Q;
+    const uint32_t* grp;  // live groups of this iteration; work item idx = (position in the list) * 32 + lane slot
+    uint32_t slot = 0;
+
+    __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
+    {
+        slot = grp[idx >> 5] * 32u + (idx & 31u);
+        if (slot >= Q.npix || !(Q.state[slot] & WF_NEXT)) return false;  // no samples left (k_regen_dense has already turned WF_TERM into WF_NEXT or 0)
+        const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
+        const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
+        wide_begin(tr, V.S, 0, o, d, ex::inf(), false);
+        return true;
+    }
+    __device__ __forceinline__ bool finish(WideTrav& tr, bool mine)
+    {
+        if (!mine) return false;
+        if (tr.hit_inst == TRAV_NONE) V.hit[slot].info = 0xffffffffu;
+        else
+        {
+            const uint32_t prim = V.S.tri_prim[tr.hit_slot];
+            V3 n;
+            bool ff;
+            finish_hit(V.S, tr.dw, tr.hit_inst, prim, tr.hit_u, tr.hit_v, &n, &ff);
+            V.hit[slot].tn = f4(tr.t_max, n.x, n.y, n.z);
+            V.hit[slot].info = tr.hit_inst | (ff ? 0x80000000u : 0u);
+        }
+        return false;
+    }
+};
+
+template <int MB>
+__global__ void __launch_bounds__(128, MB) k_extend_dense(RenderView V, Queues Q, uint32_t it, int refill_below, int node_quorum)
+{
+    WfSet& S = Q.c->set[it % 3u];
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+    {
+        Q.c->set[(it + 2u) % 3u] = WfSet{};
+        Q.c->stat_iters += 1;
+    }
+    DenseExtendJob job{V, Q, Q.grp[it & 1u]};
+    persistent_trace<0>(V.S, job, &S.cur_extend, S.n_grp * 32u, refill_below, node_quorum);
+}
+
+// Finished paths of the previous iteration, listed by k_shade_dense: accumulate the sample and start the slot's next one.
+// Runs on the list (all lanes in the regen code) rather than inside the slot-ordered extend, where the few finished slots of a
+// warp would execute it with most lanes idle.
+__global__ void __launch_bounds__(256) k_regen_dense(RenderView V, Queues Q, uint32_t it)
+{
+    const WfSet& S = Q.c->set[it % 3u];
+    const uint32_t n = S.n_term;
+    const uint32_t* list = Q.term[it & 1u];
+    unsigned long long paths = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    {
+        const uint32_t slot = list[i];
+        const uint32_t f = regen_slot(V, slot);
+        Q.state[slot] = f & WF_NEXT;
+        paths += (f & WF_NEXT) ? 1u : 0u;
+    }
+    paths = warp_sum(paths);
+    if ((threadIdx.x & 31u) == 0u && paths) atomicAdd(&Q.c->stat_paths, paths);
+}
+
+// One warp per listed group, a block takes SHADE_ROWS x 8 consecutive list entries at a time.  Two ascending lists come out, each
+// with ONE reservation per block and span (same-address atomics retire at roughly one per 2 ns on this part, so a reservation per
+// warp would bound the kernel): the slots whose path ended, for k_regen_dense, and the groups that still hold a live slot, for the
+// next iteration.  The counters double as what the host polls (live slots = continuing + ended, and the listed groups).
+constexpr uint32_t SHADE_ROWS = 8, SHADE_GROUPS = SHADE_ROWS * 8;
+__global__ void __launch_bounds__(256, 4) k_shade_dense(RenderView V, Queues Q, uint32_t it)
+{
+    const WfSet& S = Q.c->set[it % 3u];
+    WfSet& N = Q.c->set[(it + 1u) % 3u];
+    const uint32_t* grp = Q.grp[it & 1u];
+    uint32_t* grp_next = Q.grp[(it + 1u) & 1u];
+    uint32_t* term = Q.term[(it + 1u) & 1u];
+    const uint32_t n_grp = S.n_grp;
+    __shared__ uint32_t cnt_t[SHADE_GROUPS], cnt_g[SHADE_GROUPS];  // per (row, warp): ended slots / group stays listed; after the scan: exclusive prefixes
+    __shared__ uint32_t base_t, base_g, acc[2];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (threadIdx.x < 2) acc[threadIdx.x] = 0u;
+    __syncthreads();
+    uint32_t n_next = 0, n_live = 0;
+    for (uint32_t first = blockIdx.x * SHADE_GROUPS; first < n_grp; first += gridDim.x * SHADE_GROUPS)
+    {
+#pragma unroll 1
+        for (uint32_t row = 0; row < SHADE_ROWS; ++row)
+        {
+            const uint32_t gi = first + row * 8u + warp;
+            const uint32_t slot = gi < n_grp ? grp[gi] * 32u + lane : 0xffffffffu;
+            uint32_t flags = 0u;
+            if (slot < Q.npix && (Q.state[slot] & WF_NEXT))
+            {
+                flags = shade_slot(V, slot);
+                Q.state[slot] = flags;
+                ++n_live;
+                n_next += (flags & WF_NEXT) ? 1u : 0u;
+            }
+            const unsigned mt = __ballot_sync(0xffffffffu, (flags & WF_TERM) != 0u);
+            const unsigned ml = __ballot_sync(0xffffffffu, (flags & (WF_NEXT | WF_TERM)) != 0u);
+            if (lane == 0u) { cnt_t[row * 8u + warp] = (uint32_t)__popc(mt); cnt_g[row * 8u + warp] = ml ? 1u : 0u; }
+        }
+        __syncthreads();
+        if (warp < 2u)  // warp 0 scans the ended-slot counts, warp 1 the group flags (two entries per lane); one reservation each
+        {
+            uint32_t* c = warp == 0u ? cnt_t : cnt_g;
+            const uint32_t a = c[2u * lane], b = c[2u * lane + 1u];
+            uint32_t incl = a + b;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1)
+            {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                if ((int)lane >= o) incl += t;
+            }
+            const uint32_t excl = incl - (a + b);
+            c[2u * lane] = excl;
+            c[2u * lane + 1u] = excl + a;
+            if (lane == 31u)
+            {
+                const uint32_t r = incl ? atomicAdd(warp == 0u ? &N.n_term : &N.n_grp, incl) : 0u;
+                if (warp == 0u) base_t = r;
+                else base_g = r;
+            }
+        }
+        __syncthreads();
+#pragma unroll 1
+        for (uint32_t row = 0; row < SHADE_ROWS; ++row)
+        {
+            const uint32_t gi = first + row * 8u + warp;
+            const uint32_t g = gi < n_grp ? grp[gi] : 0xffffffffu;
+            const uint32_t slot = gi < n_grp ? g * 32u + lane : 0xffffffffu;
+            const uint32_t st = slot < Q.npix ? Q.state[slot] : 0u;
+            // a WF_TERM flag can only be this pass's: the pass ran on the WF_NEXT slots, and k_regen_dense had cleared every older WF_TERM
+            const unsigned mt = __ballot_sync(0xffffffffu, (st & WF_TERM) != 0u);
+            const unsigned ml = __ballot_sync(0xffffffffu, (st & (WF_NEXT | WF_TERM)) != 0u);
+            if (st & WF_TERM) term[base_t + cnt_t[row * 8u + warp] + (uint32_t)__popc(mt & ((1u << lane) - 1u))] = slot;
+            if (lane == 0u && ml) grp_next[base_g + cnt_g[row * 8u + warp]] = g;
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        n_next += __shfl_xor_sync(0xffffffffu, n_next, o);
+        n_live += __shfl_xor_sync(0xffffffffu, n_live, o);
+    }
+    if (lane == 0u) { atomicAdd(&acc[0], n_next); atomicAdd(&acc[1], n_live); }
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        if (acc[0]) atomicAdd(&N.n_cont, acc[0]);
+        if (acc[1]) atomicAdd(&Q.c->stat_extend, (unsigned long long)acc[1]);
+    }
+}
+
+struct DenseNeeJob : NeeJob
+{
+    const uint32_t* grp;
+    __device__ __forceinline__ DenseNeeJob(const RenderView& v, const Queues& q, const uint32_t* g) : NeeJob{v, q}, grp(g) {}
+    __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
+    {
+        const uint32_t s = grp[idx >> 5] * 32u + (idx & 31u);
+        if (s >= Q.npix) return false;
+        const uint32_t st = Q.state[s];
+        if (!(st & (WF_SHADOW | WF_PROBE))) return false;
+        return begin_slot(s, st & (WF_SHADOW | WF_PROBE), tr);
+    }
+};
+
+template <int MB>
+__global__ void __launch_bounds__(128, MB) k_nee_dense(RenderView V, Queues Q, uint32_t it, int refill_below, int node_quorum)
+{
+    WfSet& S = Q.c->set[it % 3u];
+    DenseNeeJob job(V, Q, Q.grp[it & 1u]);
+    persistent_trace<2>(V.S, job, &S.cur_nee, S.n_grp * 32u, refill_below, node_quorum);
+    const unsigned long long a = warp_sum(job.n_shadow), b = warp_sum(job.n_probe), c = warp_sum(job.n_probe_shadow);
+    if ((threadIdx.x & 31u) == 0u)
+    {
+        if (a) atomicAdd(&Q.c->stat_shadow, a);
+        if (b) atomicAdd(&Q.c->stat_probe, b);
+        if (c) atomicAdd(&Q.c->stat_probe_shadow, c);
+    }
+}
+
+// flag words -> cont queue of iteration `it` (its counter must be zero; the term list is already there, written by k_shade_dense)
+__global__ void __launch_bounds__(256) k_compact(Queues Q, uint32_t it)
+{
+    WfSet& S = Q.c->set[it % 3u];
+    const uint32_t b = it & 1u;
+    const uint32_t span = (Q.npix + 31u) & ~31u;
+    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < span; slot += gridDim.x * blockDim.x)
+    {
+        const uint32_t st = slot < Q.npix ? Q.state[slot] : 0u;
+        warp_push(Q.cont[b], &S.n_cont, (st & WF_NEXT) != 0u, slot);
     }
 }
 
@@ -521,7 +739,7 @@ void render_state_destroy(ptb_context* ctx)
     rs->accum_own.release(); rs->accum_sq.release(); rs->position.release();
     rs->s_accum.release(); rs->s_accum_sq.release(); rs->s_position.release(); rs->s_id.release();
     rs->ray.release(); rs->path.release(); rs->hit.release(); rs->shadow.release(); rs->probe.release();
-    DBuf<uint32_t>* u32s[] = {&rs->id, &rs->q_cont0, &rs->q_cont1, &rs->q_term0, &rs->q_term1, &rs->q_mat, &rs->q_nee};
+    DBuf<uint32_t>* u32s[] = {&rs->id, &rs->q_cont0, &rs->q_cont1, &rs->q_term0, &rs->q_term1, &rs->q_mat, &rs->q_nee, &rs->slot_state, &rs->q_grp0, &rs->q_grp1};
     for (auto* b : u32s) b->release();
     rs->volset.release();
     rs->counters.release();
@@ -635,7 +853,7 @@ int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height)
     PTB_CUDA(ctx, rs.id.resize(npix));
     if (ctx->second_moment) PTB_CUDA(ctx, rs.accum_sq.resize(npix));
     PTB_CUDA(ctx, rs.counters.resize(1));
-    if (!rs.h_flags) PTB_CUDA(ctx, cudaHostAlloc((void**)&rs.h_flags, POLL_RING * 2 * sizeof(uint32_t), cudaHostAllocDefault));
+    if (!rs.h_flags) PTB_CUDA(ctx, cudaHostAlloc((void**)&rs.h_flags, POLL_RING * 4 * sizeof(uint32_t), cudaHostAllocDefault));
     if (!rs.ev_begin) { PTB_CUDA(ctx, cudaEventCreate(&rs.ev_begin)); PTB_CUDA(ctx, cudaEventCreate(&rs.ev_end)); }
     if (!bound) rs.accum = rs.accum_own.p;
     PTB_CUDA(ctx, cudaMemsetAsync(rs.accum, 0, (size_t)npix * 16, ctx->stream));
@@ -710,10 +928,12 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     PTB_CUDA(ctx, rs.shadow.resize(n_slots));
     PTB_CUDA(ctx, rs.probe.resize(n_slots));
     {
-        DBuf<uint32_t>* u32s[] = {&rs.q_cont0, &rs.q_cont1, &rs.q_term0, &rs.q_term1, &rs.q_nee};
+        DBuf<uint32_t>* u32s[] = {&rs.q_cont0, &rs.q_cont1, &rs.q_term0, &rs.q_term1, &rs.q_nee, &rs.slot_state};
         for (auto* b : u32s) PTB_CUDA(ctx, b->resize(n_slots));
     }
     PTB_CUDA(ctx, rs.q_mat.resize(n_slots * 7));
+    PTB_CUDA(ctx, rs.q_grp0.resize((n_slots + 31) / 32));
+    PTB_CUDA(ctx, rs.q_grp1.resize((n_slots + 31) / 32));
     PTB_CUDA(ctx, rs.volset.resize(n_slots));
     rs.n_slots = (uint32_t)n_slots;
     RenderView V{};
@@ -734,7 +954,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     V.volset = ctx->scene.volumes.empty() ? nullptr : rs.volset.p;
     Queues Q{};
     Q.cont[0] = rs.q_cont0.p; Q.cont[1] = rs.q_cont1.p; Q.term[0] = rs.q_term0.p; Q.term[1] = rs.q_term1.p;
-    Q.mat = rs.q_mat.p; Q.nee = rs.q_nee.p;
+    Q.mat = rs.q_mat.p; Q.nee = rs.q_nee.p; Q.state = rs.slot_state.p; Q.grp[0] = rs.q_grp0.p; Q.grp[1] = rs.q_grp1.p;
     Q.npix = rs.n_slots;  // queue capacity and stride: one entry per slot
     Q.c = rs.counters.p;
 
@@ -780,37 +1000,71 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     const bool sort = ctx->opt_sort_materials != 0, bin = V.extend_kernel != 0u;
     const uint32_t LAG = 8;
     rs.log_iters = 0;
+    // slot-ordered kernels while the listed groups are at least dense_threshold % full of live slots (never for the reference-order variant)
+    bool dense = !bin && ctx->opt_dense != 0;
+    const uint64_t dense_pct = (uint64_t)std::max(0, std::min(100, ctx->opt_dense_threshold));
+    const int shade_grid = ctx->sm_count * 8;
     for (uint32_t it = 0;; ++it)
     {
-        if (bin) k_extend_bin<<<grid, threads, 0, st>>>(V, Q, it);
-        else
+        const int rb = ctx->opt_refill_below, nq = ctx->opt_node_quorum;
+        if (dense)
         {
-            const int g = ctx->sm_count * ctx->opt_extend_blocks, so = sort ? 1 : 0, rb = ctx->opt_refill_below;
+            const int g = ctx->sm_count * ctx->opt_extend_blocks;
+            k_regen_dense<<<shade_grid, 256, 0, st>>>(V, Q, it);
+            rs.launches += 1;
             switch (ctx->opt_extend_blocks)
             {
-            case 5: k_extend<5><<<g, threads, 0, st>>>(V, Q, it, so, rb, ctx->opt_node_quorum); break;
-            case 7: k_extend<7><<<g, threads, 0, st>>>(V, Q, it, so, rb, ctx->opt_node_quorum); break;
-            case 8: k_extend<8><<<g, threads, 0, st>>>(V, Q, it, so, rb, ctx->opt_node_quorum); break;
-            default: k_extend<6><<<ctx->sm_count * 6, threads, 0, st>>>(V, Q, it, so, rb, ctx->opt_node_quorum); break;
+            case 5: k_extend_dense<5><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
+            case 7: k_extend_dense<7><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
+            case 8: k_extend_dense<8><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
+            default: k_extend_dense<6><<<ctx->sm_count * 6, threads, 0, st>>>(V, Q, it, rb, nq); break;
             }
+            PTB_CUDA(ctx, mark(2));
+            k_shade_dense<<<shade_grid, 256, 0, st>>>(V, Q, it);
+            PTB_CUDA(ctx, mark(3));
         }
-        PTB_CUDA(ctx, mark(2));
-        k_shade<<<grid, threads, 0, st>>>(V, Q, it);
-        PTB_CUDA(ctx, mark(3));
+        else
+        {
+            if (bin) k_extend_bin<<<grid, threads, 0, st>>>(V, Q, it);
+            else
+            {
+                const int g = ctx->sm_count * ctx->opt_extend_blocks, so = sort ? 1 : 0;
+                switch (ctx->opt_extend_blocks)
+                {
+                case 5: k_extend<5><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
+                case 7: k_extend<7><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
+                case 8: k_extend<8><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
+                default: k_extend<6><<<ctx->sm_count * 6, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
+                }
+            }
+            PTB_CUDA(ctx, mark(2));
+            k_shade<<<grid, threads, 0, st>>>(V, Q, it);
+            PTB_CUDA(ctx, mark(3));
+        }
         rs.launches += 2;
         if (V.enable_nee)
         {
             if (bin) k_nee_bin<<<grid, threads, 0, st>>>(V, Q, it);
-            else
+            else if (dense)
             {
-                const int g = ctx->sm_count * ctx->opt_nee_blocks, rb = ctx->opt_refill_below;
+                const int g = ctx->sm_count * ctx->opt_nee_blocks;
                 switch (ctx->opt_nee_blocks)
                 {
-                case 5: k_nee<5><<<g, threads, 0, st>>>(V, Q, it, rb, ctx->opt_node_quorum); break;
-                case 7: k_nee<7><<<g, threads, 0, st>>>(V, Q, it, rb, ctx->opt_node_quorum); break;
-                case 8: k_nee<8><<<g, threads, 0, st>>>(V, Q, it, rb, ctx->opt_node_quorum); break;
-                case 6: k_nee<6><<<g, threads, 0, st>>>(V, Q, it, rb, ctx->opt_node_quorum); break;
-                default: k_nee<5><<<ctx->sm_count * 5, threads, 0, st>>>(V, Q, it, rb, ctx->opt_node_quorum); break;
+                case 7: k_nee_dense<7><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
+                case 8: k_nee_dense<8><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
+                case 6: k_nee_dense<6><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
+                default: k_nee_dense<5><<<ctx->sm_count * 5, threads, 0, st>>>(V, Q, it, rb, nq); break;
+                }
+            }
+            else
+            {
+                const int g = ctx->sm_count * ctx->opt_nee_blocks;
+                switch (ctx->opt_nee_blocks)
+                {
+                case 7: k_nee<7><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
+                case 8: k_nee<8><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
+                case 6: k_nee<6><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
+                default: k_nee<5><<<ctx->sm_count * 5, threads, 0, st>>>(V, Q, it, rb, nq); break;
                 }
             }
             PTB_CUDA(ctx, mark(4));
@@ -818,16 +1072,26 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         }
         PTB_CUDA(ctx, cudaGetLastError());
         // active-slot count of the next iteration, read LAG iterations behind the launch front
-        PTB_CUDA(ctx, cudaMemcpyAsync(&rs.h_flags[(it % POLL_RING) * 2], &rs.counters.p->set[(it + 1u) % 3u].n_cont, 8, cudaMemcpyDeviceToHost, st));
+        PTB_CUDA(ctx, cudaMemcpyAsync(&rs.h_flags[(it % POLL_RING) * 4], &rs.counters.p->set[(it + 1u) % 3u].n_cont, 16, cudaMemcpyDeviceToHost, st));
         PTB_CUDA(ctx, cudaEventRecord(rs.poll_events[it % NEV], st));
         rs.log_iters = it + 1;
         if (it >= LAG)
         {
             PTB_CUDA(ctx, cudaEventSynchronize(rs.poll_events[(it - LAG) % NEV]));
-            const uint32_t* f = &rs.h_flags[((it - LAG) % POLL_RING) * 2];
+            const uint32_t* f = &rs.h_flags[((it - LAG) % POLL_RING) * 4];
             const uint32_t active = f[0] + f[1];
             if (active == 0u) break;
-            if (active <= tail_threshold)
+            const bool to_tail = active <= tail_threshold;
+            if (dense && (to_tail || (uint64_t)active * 100u < dense_pct * 32u * (uint64_t)f[3]))
+            {
+                // continue sparse: rebuild the cont queue of iteration it+1 from the flag words (its counter so far only held the live count)
+                PTB_CUDA(ctx, cudaMemsetAsync(&rs.counters.p->set[(it + 1u) % 3u].n_cont, 0, 4, st));
+                k_compact<<<shade_grid, 256, 0, st>>>(Q, it + 1u);
+                PTB_CUDA(ctx, cudaGetLastError());
+                rs.launches += 1;
+                dense = false;
+            }
+            if (to_tail)
             {
                 if (bin) k_tail<true><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);
                 else k_tail<false><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);  // active counts never grow: `active` bounds the queue at it+1
@@ -868,7 +1132,7 @@ int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active,
     if (!ctx->rs || !count) return ctx->fail(PTB_ERR_INVALID, "no frame");
     const uint32_t n = std::min<uint32_t>(std::min<uint32_t>(ctx->rs->log_iters, POLL_RING), capacity);
     PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    for (uint32_t i = 0; i < n && active; ++i) active[i] = ctx->rs->h_flags[i * 2] + ctx->rs->h_flags[i * 2 + 1];
+    for (uint32_t i = 0; i < n && active; ++i) active[i] = ctx->rs->h_flags[i * 4] + ctx->rs->h_flags[i * 4 + 1];
     *count = n;
     return PTB_OK;
 }
