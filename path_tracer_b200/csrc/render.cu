@@ -175,7 +175,7 @@ struct ExtendJob
     const Queues& Q;
     WfSet& S;
     uint32_t b, n_cont, n_term;
-    bool sort;
+    int sort;  // 1: push the slot to the shade queue of its material kind, 0: to queue 0, -1: no push (k_shade_ordered walks the slots itself)
     uint32_t slot = 0;
     unsigned long long paths = 0;
 
@@ -192,7 +192,9 @@ struct ExtendJob
         else
         {
             slot = Q.term[b][idx - n_cont];
-            if (!(regen_slot(V, slot, &o, &d) & WF_NEXT)) return false;
+            const uint32_t f = regen_slot(V, slot, &o, &d) & WF_NEXT;
+            Q.state[slot] = f;  // live (a ray is being traced for it this iteration) or out of samples
+            if (!f) return false;
             ++paths;
         }
         wide_begin(tr, V.S, 0, o, d, ex::inf(), false);
@@ -218,9 +220,9 @@ struct ExtendJob
                 V.hit[slot].info = tr.hit_inst | (ff ? 0x80000000u : 0u);
                 kind = V.S.mat[V.S.inst[tr.hit_inst].blas].kind;
             }
-            if (!sort) kind = 0u;
+            if (sort == 0) kind = 0u;
         }
-        warp_push_keyed(Q.mat, Q.npix, S.n_mat, kind, slot);
+        if (sort >= 0) warp_push_keyed(Q.mat, Q.npix, S.n_mat, kind, slot);
         return false;
     }
 };
@@ -235,7 +237,7 @@ __global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint
         Q.c->set[(it + 2u) % 3u] = WfSet{};  // consumed in iteration it-1, refilled from iteration it+1 on
         if (n_cont + n_term) Q.c->stat_iters += 1;
     }
-    ExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort != 0};
+    ExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort};
     persistent_trace<0>(V.S, job, &S.cur_extend, n_cont + n_term, refill_below, node_quorum);
     const unsigned long long p = warp_sum(job.paths);
     if ((threadIdx.x & 31u) == 0u && p) atomicAdd(&Q.c->stat_paths, p);
@@ -430,100 +432,34 @@ __global__ void __launch_bounds__(128) k_nee_bin(RenderView V, Queues Q, uint32_
     }
 }
 
-// ---- slot-ordered ("dense") wavefront --------------------------------------------------------------------------------------
-// While most slots carry a live path (path regeneration keeps them busy until their samples run out) the queues buy nothing:
-// every slot has exactly one ray per iteration.  These kernels walk the slots in index order instead and keep a per-slot flag
-// word (Q.state = the WF_* flags of the slot's last shade):  no queue pushes, no atomics on the dependency chain, and all
-// per-slot records are read and written in address order (consecutive lanes = consecutive 32-byte records).  The unit of work
-// is a GROUP of 32 consecutive slots; k_shade_dense keeps an ascending list of the groups that still hold a live slot, so regions
-// of the image whose samples are exhausted (background pixels finish their samples long before the others) cost nothing.  The
-// host watches live slots / (32 x listed groups) and continues with the queue kernels (k_compact, then k_extend ... k_tail) once
-// the live slots are scattered thinly over the groups.
-struct DenseExtendJob
-{
-    const RenderView& V;
-    const Queues& Q;
-    const uint32_t* grp;  // live groups of this iteration; work item idx = (position in the list) * 32 + lane slot
-    uint32_t slot = 0;
-
-    __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
-    {
-        slot = grp[idx >> 5] * 32u + (idx & 31u);
-        if (slot >= Q.npix || !(Q.state[slot] & WF_NEXT)) return false;  // no samples left (k_regen_dense has already turned WF_TERM into WF_NEXT or 0)
-        const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
-        const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
-        wide_begin(tr, V.S, 0, o, d, ex::inf(), false);
-        return true;
-    }
-    __device__ __forceinline__ bool finish(WideTrav& tr, bool mine)
-    {
-        if (!mine) return false;
-        if (tr.hit_inst == TRAV_NONE) V.hit[slot].info = 0xffffffffu;
-        else
-        {
-            const uint32_t prim = V.S.tri_prim[tr.hit_slot];
-            V3 n;
-            bool ff;
-            finish_hit(V.S, tr.dw, tr.hit_inst, prim, tr.hit_u, tr.hit_v, &n, &ff);
-            V.hit[slot].tn = f4(tr.t_max, n.x, n.y, n.z);
-            V.hit[slot].info = tr.hit_inst | (ff ? 0x80000000u : 0u);
-        }
-        return false;
-    }
-};
-
-template <int MB>
-__global__ void __launch_bounds__(128, MB) k_extend_dense(RenderView V, Queues Q, uint32_t it, int refill_below, int node_quorum)
+// ---- slot-ordered shading ------------------------------------------------------------------------------------------------
+// k_shade (above) takes its work from queues that k_extend fills in completion order: every queue push is an atomicAdd whose
+// return value the warp waits for (four per 32 slots, on four hot addresses: 47 % of its stall samples, profiles/r1d_c2_*), and
+// the queues it writes are in scrambled order, so the next kernels touch the 32-byte per-slot records as scattered sectors.
+// k_shade_ordered walks the slots in index order instead (one warp per GROUP of 32 consecutive slots, only the groups that still
+// hold a live slot) and writes all four outputs as ASCENDING lists with one reservation per block and span of 64 groups:
+//   cont / term  the queues of the next k_extend,     nee  the queue of this iteration's k_nee,     grp  its own next work list.
+// k_extend and k_nee are the queue kernels unchanged (k_extend just does not push, sort = -1); with ascending queues their
+// record accesses are near-sequential.  Q.state holds one flag word per slot: WF_NEXT while a ray was traced for the slot in this
+// iteration (set by the previous shade or by k_extend's regeneration), so that the walk knows which lanes of a group have a hit
+// record.  The host may switch between the two shade kernels at any iteration: both leave valid cont / term / nee queues.
+constexpr uint32_t SHADE_ROWS = 8, SHADE_GROUPS = SHADE_ROWS * 8;
+__global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q, uint32_t it)
 {
     WfSet& S = Q.c->set[it % 3u];
-    if (blockIdx.x == 0 && threadIdx.x == 0)
-    {
-        Q.c->set[(it + 2u) % 3u] = WfSet{};
-        Q.c->stat_iters += 1;
-    }
-    DenseExtendJob job{V, Q, Q.grp[it & 1u]};
-    persistent_trace<0>(V.S, job, &S.cur_extend, S.n_grp * 32u, refill_below, node_quorum);
-}
-
-// Finished paths of the previous iteration, listed by k_shade_dense: accumulate the sample and start the slot's next one.
-// Runs on the list (all lanes in the regen code) rather than inside the slot-ordered extend, where the few finished slots of a
-// warp would execute it with most lanes idle.
-__global__ void __launch_bounds__(256) k_regen_dense(RenderView V, Queues Q, uint32_t it)
-{
-    const WfSet& S = Q.c->set[it % 3u];
-    const uint32_t n = S.n_term;
-    const uint32_t* list = Q.term[it & 1u];
-    unsigned long long paths = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    {
-        const uint32_t slot = list[i];
-        const uint32_t f = regen_slot(V, slot);
-        Q.state[slot] = f & WF_NEXT;
-        paths += (f & WF_NEXT) ? 1u : 0u;
-    }
-    paths = warp_sum(paths);
-    if ((threadIdx.x & 31u) == 0u && paths) atomicAdd(&Q.c->stat_paths, paths);
-}
-
-// One warp per listed group, a block takes SHADE_ROWS x 8 consecutive list entries at a time.  Two ascending lists come out, each
-// with ONE reservation per block and span (same-address atomics retire at roughly one per 2 ns on this part, so a reservation per
-// warp would bound the kernel): the slots whose path ended, for k_regen_dense, and the groups that still hold a live slot, for the
-// next iteration.  The counters double as what the host polls (live slots = continuing + ended, and the listed groups).
-constexpr uint32_t SHADE_ROWS = 8, SHADE_GROUPS = SHADE_ROWS * 8;
-__global__ void __launch_bounds__(256, 4) k_shade_dense(RenderView V, Queues Q, uint32_t it)
-{
-    const WfSet& S = Q.c->set[it % 3u];
     WfSet& N = Q.c->set[(it + 1u) % 3u];
+    const uint32_t nb = (it + 1u) & 1u;
     const uint32_t* grp = Q.grp[it & 1u];
-    uint32_t* grp_next = Q.grp[(it + 1u) & 1u];
-    uint32_t* term = Q.term[(it + 1u) & 1u];
+    uint32_t* out[4] = {Q.term[nb], Q.cont[nb], Q.nee, Q.grp[nb]};
+    uint32_t* out_n[4] = {&N.n_term, &N.n_cont, &S.n_nee, &N.n_grp};
     const uint32_t n_grp = S.n_grp;
-    __shared__ uint32_t cnt_t[SHADE_GROUPS], cnt_g[SHADE_GROUPS];  // per (row, warp): ended slots / group stays listed; after the scan: exclusive prefixes
-    __shared__ uint32_t base_t, base_g, acc[2];
+    // per list and (row, warp): entries of that warp-row; after the scan: exclusive prefix within the span
+    __shared__ uint32_t cnt[4][SHADE_GROUPS];
+    __shared__ uint32_t base[4], live_total;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    if (threadIdx.x < 2) acc[threadIdx.x] = 0u;
+    if (threadIdx.x == 0) live_total = 0u;
     __syncthreads();
-    uint32_t n_next = 0, n_live = 0;
+    uint32_t n_live = 0;
     for (uint32_t first = blockIdx.x * SHADE_GROUPS; first < n_grp; first += gridDim.x * SHADE_GROUPS)
     {
 #pragma unroll 1
@@ -535,18 +471,21 @@ __global__ void __launch_bounds__(256, 4) k_shade_dense(RenderView V, Queues Q, 
             if (slot < Q.npix && (Q.state[slot] & WF_NEXT))
             {
                 flags = shade_slot(V, slot);
-                Q.state[slot] = flags;
                 ++n_live;
-                n_next += (flags & WF_NEXT) ? 1u : 0u;
             }
-            const unsigned mt = __ballot_sync(0xffffffffu, (flags & WF_TERM) != 0u);
-            const unsigned ml = __ballot_sync(0xffffffffu, (flags & (WF_NEXT | WF_TERM)) != 0u);
-            if (lane == 0u) { cnt_t[row * 8u + warp] = (uint32_t)__popc(mt); cnt_g[row * 8u + warp] = ml ? 1u : 0u; }
+            if (slot < Q.npix) Q.state[slot] = flags;
+            const unsigned mt = __ballot_sync(0xffffffffu, (flags & WF_TERM) != 0u), mc = __ballot_sync(0xffffffffu, (flags & WF_NEXT) != 0u);
+            const unsigned mn = __ballot_sync(0xffffffffu, (flags & (WF_SHADOW | WF_PROBE)) != 0u);
+            if (lane == 0u)
+            {
+                const uint32_t e = row * 8u + warp;
+                cnt[0][e] = (uint32_t)__popc(mt); cnt[1][e] = (uint32_t)__popc(mc); cnt[2][e] = (uint32_t)__popc(mn); cnt[3][e] = (mt | mc) ? 1u : 0u;
+            }
         }
         __syncthreads();
-        if (warp < 2u)  // warp 0 scans the ended-slot counts, warp 1 the group flags (two entries per lane); one reservation each
+        if (warp < 4u)  // warp w scans list w (64 counts, two per lane) and makes the span's one reservation on that list's counter
         {
-            uint32_t* c = warp == 0u ? cnt_t : cnt_g;
+            uint32_t* c = cnt[warp];
             const uint32_t a = c[2u * lane], b = c[2u * lane + 1u];
             uint32_t incl = a + b;
 #pragma unroll
@@ -558,84 +497,32 @@ __global__ void __launch_bounds__(256, 4) k_shade_dense(RenderView V, Queues Q, 
             const uint32_t excl = incl - (a + b);
             c[2u * lane] = excl;
             c[2u * lane + 1u] = excl + a;
-            if (lane == 31u)
-            {
-                const uint32_t r = incl ? atomicAdd(warp == 0u ? &N.n_term : &N.n_grp, incl) : 0u;
-                if (warp == 0u) base_t = r;
-                else base_g = r;
-            }
+            if (lane == 31u) base[warp] = incl ? atomicAdd(out_n[warp], incl) : 0u;
         }
         __syncthreads();
 #pragma unroll 1
         for (uint32_t row = 0; row < SHADE_ROWS; ++row)
         {
-            const uint32_t gi = first + row * 8u + warp;
+            const uint32_t gi = first + row * 8u + warp, e = row * 8u + warp;
             const uint32_t g = gi < n_grp ? grp[gi] : 0xffffffffu;
             const uint32_t slot = gi < n_grp ? g * 32u + lane : 0xffffffffu;
-            const uint32_t st = slot < Q.npix ? Q.state[slot] : 0u;
-            // a WF_TERM flag can only be this pass's: the pass ran on the WF_NEXT slots, and k_regen_dense had cleared every older WF_TERM
-            const unsigned mt = __ballot_sync(0xffffffffu, (st & WF_TERM) != 0u);
-            const unsigned ml = __ballot_sync(0xffffffffu, (st & (WF_NEXT | WF_TERM)) != 0u);
-            if (st & WF_TERM) term[base_t + cnt_t[row * 8u + warp] + (uint32_t)__popc(mt & ((1u << lane) - 1u))] = slot;
-            if (lane == 0u && ml) grp_next[base_g + cnt_g[row * 8u + warp]] = g;
+            const uint32_t flags = slot < Q.npix ? Q.state[slot] : 0u;  // written by this thread in the first pass
+            const unsigned lt = (1u << lane) - 1u;
+            const unsigned mt = __ballot_sync(0xffffffffu, (flags & WF_TERM) != 0u), mc = __ballot_sync(0xffffffffu, (flags & WF_NEXT) != 0u);
+            const unsigned mn = __ballot_sync(0xffffffffu, (flags & (WF_SHADOW | WF_PROBE)) != 0u);
+            if (flags & WF_TERM) out[0][base[0] + cnt[0][e] + (uint32_t)__popc(mt & lt)] = slot;
+            if (flags & WF_NEXT) out[1][base[1] + cnt[1][e] + (uint32_t)__popc(mc & lt)] = slot;
+            if (flags & (WF_SHADOW | WF_PROBE))
+                out[2][base[2] + cnt[2][e] + (uint32_t)__popc(mn & lt)] = slot | ((flags & WF_SHADOW) ? NEE_SHADOW_BIT : 0u) | ((flags & WF_PROBE) ? NEE_PROBE_BIT : 0u);
+            if (lane == 0u && (mt | mc)) out[3][base[3] + cnt[3][e]] = g;
         }
         __syncthreads();
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
-    {
-        n_next += __shfl_xor_sync(0xffffffffu, n_next, o);
-        n_live += __shfl_xor_sync(0xffffffffu, n_live, o);
-    }
-    if (lane == 0u) { atomicAdd(&acc[0], n_next); atomicAdd(&acc[1], n_live); }
+    for (int o = 16; o > 0; o >>= 1) n_live += __shfl_xor_sync(0xffffffffu, n_live, o);
+    if (lane == 0u && n_live) atomicAdd(&live_total, n_live);
     __syncthreads();
-    if (threadIdx.x == 0)
-    {
-        if (acc[0]) atomicAdd(&N.n_cont, acc[0]);
-        if (acc[1]) atomicAdd(&Q.c->stat_extend, (unsigned long long)acc[1]);
-    }
-}
-
-struct DenseNeeJob : NeeJob
-{
-    const uint32_t* grp;
-    __device__ __forceinline__ DenseNeeJob(const RenderView& v, const Queues& q, const uint32_t* g) : NeeJob{v, q}, grp(g) {}
-    __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
-    {
-        const uint32_t s = grp[idx >> 5] * 32u + (idx & 31u);
-        if (s >= Q.npix) return false;
-        const uint32_t st = Q.state[s];
-        if (!(st & (WF_SHADOW | WF_PROBE))) return false;
-        return begin_slot(s, st & (WF_SHADOW | WF_PROBE), tr);
-    }
-};
-
-template <int MB>
-__global__ void __launch_bounds__(128, MB) k_nee_dense(RenderView V, Queues Q, uint32_t it, int refill_below, int node_quorum)
-{
-    WfSet& S = Q.c->set[it % 3u];
-    DenseNeeJob job(V, Q, Q.grp[it & 1u]);
-    persistent_trace<2>(V.S, job, &S.cur_nee, S.n_grp * 32u, refill_below, node_quorum);
-    const unsigned long long a = warp_sum(job.n_shadow), b = warp_sum(job.n_probe), c = warp_sum(job.n_probe_shadow);
-    if ((threadIdx.x & 31u) == 0u)
-    {
-        if (a) atomicAdd(&Q.c->stat_shadow, a);
-        if (b) atomicAdd(&Q.c->stat_probe, b);
-        if (c) atomicAdd(&Q.c->stat_probe_shadow, c);
-    }
-}
-
-// flag words -> cont queue of iteration `it` (its counter must be zero; the term list is already there, written by k_shade_dense)
-__global__ void __launch_bounds__(256) k_compact(Queues Q, uint32_t it)
-{
-    WfSet& S = Q.c->set[it % 3u];
-    const uint32_t b = it & 1u;
-    const uint32_t span = (Q.npix + 31u) & ~31u;
-    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < span; slot += gridDim.x * blockDim.x)
-    {
-        const uint32_t st = slot < Q.npix ? Q.state[slot] : 0u;
-        warp_push(Q.cont[b], &S.n_cont, (st & WF_NEXT) != 0u, slot);
-    }
+    if (threadIdx.x == 0 && live_total) atomicAdd(&Q.c->stat_extend, (unsigned long long)live_total);
 }
 
 // The tail: one thread per remaining slot runs regen -> extend -> shade -> shadow -> probe until the slot has no samples left.
@@ -1000,62 +887,33 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     const bool sort = ctx->opt_sort_materials != 0, bin = V.extend_kernel != 0u;
     const uint32_t LAG = 8;
     rs.log_iters = 0;
-    // slot-ordered kernels while the listed groups are at least dense_threshold % full of live slots (never for the reference-order variant)
+    // k_shade_ordered while the listed groups are at least dense_threshold % full of live slots (never for the reference-order variant)
     bool dense = !bin && ctx->opt_dense != 0;
     const uint64_t dense_pct = (uint64_t)std::max(0, std::min(100, ctx->opt_dense_threshold));
     const int shade_grid = ctx->sm_count * 8;
     for (uint32_t it = 0;; ++it)
     {
         const int rb = ctx->opt_refill_below, nq = ctx->opt_node_quorum;
-        if (dense)
-        {
-            const int g = ctx->sm_count * ctx->opt_extend_blocks;
-            k_regen_dense<<<shade_grid, 256, 0, st>>>(V, Q, it);
-            rs.launches += 1;
-            switch (ctx->opt_extend_blocks)
-            {
-            case 5: k_extend_dense<5><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
-            case 7: k_extend_dense<7><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
-            case 8: k_extend_dense<8><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
-            default: k_extend_dense<6><<<ctx->sm_count * 6, threads, 0, st>>>(V, Q, it, rb, nq); break;
-            }
-            PTB_CUDA(ctx, mark(2));
-            k_shade_dense<<<shade_grid, 256, 0, st>>>(V, Q, it);
-            PTB_CUDA(ctx, mark(3));
-        }
+        if (bin) k_extend_bin<<<grid, threads, 0, st>>>(V, Q, it);
         else
         {
-            if (bin) k_extend_bin<<<grid, threads, 0, st>>>(V, Q, it);
-            else
+            const int g = ctx->sm_count * ctx->opt_extend_blocks, so = dense ? -1 : (sort ? 1 : 0);
+            switch (ctx->opt_extend_blocks)
             {
-                const int g = ctx->sm_count * ctx->opt_extend_blocks, so = sort ? 1 : 0;
-                switch (ctx->opt_extend_blocks)
-                {
-                case 5: k_extend<5><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
-                case 7: k_extend<7><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
-                case 8: k_extend<8><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
-                default: k_extend<6><<<ctx->sm_count * 6, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
-                }
+            case 5: k_extend<5><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
+            case 7: k_extend<7><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
+            case 8: k_extend<8><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
+            default: k_extend<6><<<ctx->sm_count * 6, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
             }
-            PTB_CUDA(ctx, mark(2));
-            k_shade<<<grid, threads, 0, st>>>(V, Q, it);
-            PTB_CUDA(ctx, mark(3));
         }
+        PTB_CUDA(ctx, mark(2));
+        if (dense) k_shade_ordered<<<shade_grid, 256, 0, st>>>(V, Q, it);
+        else k_shade<<<grid, threads, 0, st>>>(V, Q, it);
+        PTB_CUDA(ctx, mark(3));
         rs.launches += 2;
         if (V.enable_nee)
         {
             if (bin) k_nee_bin<<<grid, threads, 0, st>>>(V, Q, it);
-            else if (dense)
-            {
-                const int g = ctx->sm_count * ctx->opt_nee_blocks;
-                switch (ctx->opt_nee_blocks)
-                {
-                case 7: k_nee_dense<7><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
-                case 8: k_nee_dense<8><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
-                case 6: k_nee_dense<6><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
-                default: k_nee_dense<5><<<ctx->sm_count * 5, threads, 0, st>>>(V, Q, it, rb, nq); break;
-                }
-            }
             else
             {
                 const int g = ctx->sm_count * ctx->opt_nee_blocks;
@@ -1082,15 +940,8 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             const uint32_t active = f[0] + f[1];
             if (active == 0u) break;
             const bool to_tail = active <= tail_threshold;
-            if (dense && (to_tail || (uint64_t)active * 100u < dense_pct * 32u * (uint64_t)f[3]))
-            {
-                // continue sparse: rebuild the cont queue of iteration it+1 from the flag words (its counter so far only held the live count)
-                PTB_CUDA(ctx, cudaMemsetAsync(&rs.counters.p->set[(it + 1u) % 3u].n_cont, 0, 4, st));
-                k_compact<<<shade_grid, 256, 0, st>>>(Q, it + 1u);
-                PTB_CUDA(ctx, cudaGetLastError());
-                rs.launches += 1;
-                dense = false;
-            }
+            // live slots scattered thinly over the listed groups: the queue shade kernel from the next iteration on (the queues are valid as they are)
+            if (dense && (uint64_t)active * 100u < dense_pct * 32u * (uint64_t)f[3]) dense = false;
             if (to_tail)
             {
                 if (bin) k_tail<true><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);
