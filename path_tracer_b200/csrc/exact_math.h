@@ -142,6 +142,16 @@ PTB_HD bool tri_hit(const float n0[4], const float n1[4], const float n2[4], V3 
     *v = div(r[2], r[3]);
     return true;
 }
+// the same with the barycentric divisions left to the caller: t as above, raw = (ud, vd, det); u = ud / det, v = vd / det.
+// A closest-hit search replaces its candidate several times per ray and only the last one's (u, v) is ever used.
+PTB_HD bool tri_hit_raw(const float n0[4], const float n1[4], const float n2[4], V3 o, V3 d, float t_max, float t_est, float* t, float raw[3])
+{
+    float r[4];
+    if (!tri_naive(n0, n1, n2, ray_at(o, d, t_est), d, sub(EPS, t_est), sub(t_max, t_est), r)) return false;
+    *t = add(div(r[0], r[3]), t_est);
+    raw[0] = r[1]; raw[1] = r[2]; raw[2] = r[3];
+    return true;
+}
 PTB_HD bool tri_hit_bool(const float n0[4], const float n1[4], const float n2[4], V3 o, V3 d, float t_max, float t_est)  // primitive.rs:181-189
 {
     float r[4];

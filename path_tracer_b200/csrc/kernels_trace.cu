@@ -50,7 +50,7 @@ struct TraceJob
     {
         if (!mine) return false;
         Hit h;
-        h.t = tr.t_max; h.u = tr.hit_u; h.v = tr.hit_v; h.slot_or_prim = tr.hit_slot; h.inst = tr.hit_inst;
+        h.t = tr.t_max; h.u = wide_hit_u(tr); h.v = wide_hit_v(tr); h.slot_or_prim = tr.hit_slot; h.inst = tr.hit_inst;
         write_result(S, which, a, i, ANY, tr.hit_inst != TRAV_NONE, h, 1u, tr.dw);
         return false;
     }

@@ -215,7 +215,7 @@ struct ExtendJob
                 const uint32_t prim = V.S.tri_prim[tr.hit_slot];
                 V3 n;
                 bool ff;
-                finish_hit(V.S, tr.dw, tr.hit_inst, prim, tr.hit_u, tr.hit_v, &n, &ff);
+                finish_hit(V.S, tr.dw, tr.hit_inst, prim, wide_hit_u(tr), wide_hit_v(tr), &n, &ff);
                 V.hit[slot].tn = f4(tr.t_max, n.x, n.y, n.z);
                 V.hit[slot].info = tr.hit_inst | (ff ? 0x80000000u : 0u);
                 kind = V.S.mat[V.S.inst[tr.hit_inst].blas].kind;
@@ -377,7 +377,7 @@ struct NeeJob
         {
             if (tr.hit_inst != TRAV_NONE)
             {
-                lt = tr.t_max; lu = tr.hit_u; lv = tr.hit_v; lslot = tr.hit_slot; linst = tr.hit_inst;
+                lt = tr.t_max; lu = wide_hit_u(tr); lv = wide_hit_v(tr); lslot = tr.hit_slot; linst = tr.hit_inst;
                 wide_begin(tr, V.S, 0, o, tr.dw, lt * (1.0f - ex::EPS), true);
                 stage = 2;
                 ++n_probe_shadow;

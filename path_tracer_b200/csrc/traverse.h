@@ -192,11 +192,13 @@ struct WideTrav
     uint32_t lmask, leaf_base;
     uint32_t tri_i, tri_end;  // triangle slots of the current leaf still to test
     float t_enter;
-    float hit_u, hit_v;
+    float hit_ud, hit_vd, hit_det;  // winner's undivided barycentrics (u = ud / det, v = vd / det: wide_hit_u / wide_hit_v)
     uint32_t hit_slot, hit_inst;  // hit_inst == TRAV_NONE: nothing found yet
     uint32_t any;       // any-hit query (TLAS::any_intersect) — used when the step is instantiated with MODE == 2
 };
 
+PTB_HD float wide_hit_u(const WideTrav& s) { return ex::div(s.hit_ud, s.hit_det); }
+PTB_HD float wide_hit_v(const WideTrav& s) { return ex::div(s.hit_vd, s.hit_det); }
 PTB_HD void wide_begin(WideTrav& s, const SceneDev& S, int which, V3 o, V3 d, float t_max, bool any)
 {
     s.ow = o;
@@ -217,7 +219,8 @@ PTB_HD void wide_begin(WideTrav& s, const SceneDev& S, int which, V3 o, V3 d, fl
     s.tri_i = 0;
     s.tri_end = 0;
     s.t_enter = 0.0f;
-    s.hit_u = s.hit_v = 0.0f;
+    s.hit_ud = s.hit_vd = 0.0f;
+    s.hit_det = 1.0f;
     s.hit_slot = 0;
     s.hit_inst = TRAV_NONE;
     s.any = any ? 1u : 0u;
@@ -390,11 +393,11 @@ PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, uint2* stack, bool al
         }
         else
         {
-            float t, u, v;
-            if (ex::tri_hit(n0, n1, n2, s.ray.o, s.ray.d, s.t_max, s.t_enter, &t, &u, &v))
+            float t, raw[3];
+            if (ex::tri_hit_raw(n0, n1, n2, s.ray.o, s.ray.d, s.t_max, s.t_enter, &t, raw))
             {
                 s.t_max = t;
-                s.hit_u = u; s.hit_v = v; s.hit_slot = s.tri_i; s.hit_inst = s.cur_inst;
+                s.hit_ud = raw[0]; s.hit_vd = raw[1]; s.hit_det = raw[2]; s.hit_slot = s.tri_i; s.hit_inst = s.cur_inst;
             }
         }
         ++s.tri_i;
@@ -416,7 +419,7 @@ PTB_HD bool wide_traverse(const SceneDev& S, int which, V3 o_world, V3 d_world, 
     wide_begin(s, S, which, o_world, d_world, t_max, ANY);
     while (wide_step<ANY ? 1 : 0>(s, S, stack)) {}
     if (s.hit_inst == TRAV_NONE) return false;
-    if (!ANY) { hit->t = s.t_max; hit->u = s.hit_u; hit->v = s.hit_v; hit->slot_or_prim = s.hit_slot; hit->inst = s.hit_inst; }
+    if (!ANY) { hit->t = s.t_max; hit->u = wide_hit_u(s); hit->v = wide_hit_v(s); hit->slot_or_prim = s.hit_slot; hit->inst = s.hit_inst; }
     return true;
 }
 
