@@ -352,7 +352,7 @@ int ptb_trace_resident(ptb_context* ctx, int which, int kernel, int any_hit, int
     PTB_CUDA(ctx, cudaEventCreate(&e1));
     TraceArgs a = trace_args(ctx);
     PTB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
-    for (int r = 0; r < repeats; ++r) PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, any_hit, ctx->t_n, a, ctx->sm_count, ctx->stream, ctx->opt_refill_below, ctx->opt_node_quorum));
+    for (int r = 0; r < repeats; ++r) PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, any_hit, ctx->t_n, a, ctx->sm_count, ctx->stream, any_hit ? ctx->opt_nee_refill_below : ctx->opt_refill_below, ctx->opt_node_quorum));
     PTB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
     PTB_CUDA(ctx, cudaEventSynchronize(e1));
     float ms = 0;
@@ -413,7 +413,7 @@ int ptb_trace_any(ptb_context* ctx, int which, int kernel, uint64_t n, const flo
     if (n == 0) return PTB_OK;
     int rc = ptb_trace_upload(ctx, n, o3, d3, tmax);
     if (rc != PTB_OK) return rc;
-    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 1, n, trace_args(ctx), ctx->sm_count, ctx->stream, ctx->opt_refill_below, ctx->opt_node_quorum));
+    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 1, n, trace_args(ctx), ctx->sm_count, ctx->stream, ctx->opt_nee_refill_below, ctx->opt_node_quorum));
     PTB_CUDA(ctx, cudaMemcpyAsync(hit, ctx->t_hit.p, n, cudaMemcpyDeviceToHost, ctx->stream));
     PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return PTB_OK;
@@ -435,6 +435,7 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "tail_threshold") ctx->opt_tail_threshold = value;
     else if (n == "dense") ctx->opt_dense = value;
     else if (n == "dense_threshold") ctx->opt_dense_threshold = value;
+    else if (n == "nee_refill_below") ctx->opt_nee_refill_below = value < 1 ? 1 : (value > 32 ? 32 : value);
     else if (n == "refill_below") ctx->opt_refill_below = value < 1 ? 1 : (value > 32 ? 32 : value);
     else return ctx->fail(PTB_ERR_INVALID, "unknown option " + n);
     return PTB_OK;

@@ -726,7 +726,7 @@ int ptb_enable_second_moment(ptb_context* ctx, int enable)
 int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height)
 {
     REQUIRE_DEVICE(ctx);
-    if (width == 0 || height == 0 || (uint64_t)width * height > (uint64_t)NEE_SLOT_MASK / 8u) return ctx->fail(PTB_ERR_INVALID, "bad frame size");
+    if (width == 0 || height == 0 || (uint64_t)width * height > (uint64_t)NEE_SLOT_MASK / 16u) return ctx->fail(PTB_ERR_INVALID, "bad frame size");
     PTB_CUDA(ctx, cudaSetDevice(ctx->device));
     const bool fresh = ctx->rs == nullptr;
     if (fresh) ctx->rs = new RenderState();
@@ -802,7 +802,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     PTB_CUDA(ctx, cudaSetDevice(ctx->device));
     RenderState& rs = *ctx->rs;
     // K slots per pixel (never more than samples, so every slot renders at least one)
-    const uint32_t K = std::max(1u, std::min<uint32_t>(std::min<uint32_t>((uint32_t)std::max(1, ctx->opt_slots_per_pixel), 8u), sample_count));
+    const uint32_t K = std::max(1u, std::min<uint32_t>(std::min<uint32_t>((uint32_t)std::max(1, ctx->opt_slots_per_pixel), 16u), sample_count));
     const size_t n_slots = (size_t)rs.npix * K;
     if (n_slots > (size_t)NEE_SLOT_MASK) return ctx->fail(PTB_ERR_UNSUPPORTED, "too many path slots");
     PTB_CUDA(ctx, rs.s_accum.resize(n_slots));
@@ -893,7 +893,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     const int shade_grid = ctx->sm_count * 8;
     for (uint32_t it = 0;; ++it)
     {
-        const int rb = ctx->opt_refill_below, nq = ctx->opt_node_quorum;
+        const int rb = ctx->opt_refill_below, rbn = ctx->opt_nee_refill_below, nq = ctx->opt_node_quorum;
         if (bin) k_extend_bin<<<grid, threads, 0, st>>>(V, Q, it);
         else
         {
@@ -919,10 +919,10 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
                 const int g = ctx->sm_count * ctx->opt_nee_blocks;
                 switch (ctx->opt_nee_blocks)
                 {
-                case 7: k_nee<7><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
-                case 8: k_nee<8><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
-                case 6: k_nee<6><<<g, threads, 0, st>>>(V, Q, it, rb, nq); break;
-                default: k_nee<5><<<ctx->sm_count * 5, threads, 0, st>>>(V, Q, it, rb, nq); break;
+                case 7: k_nee<7><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
+                case 8: k_nee<8><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
+                case 6: k_nee<6><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
+                default: k_nee<5><<<ctx->sm_count * 5, threads, 0, st>>>(V, Q, it, rbn, nq); break;
                 }
             }
             PTB_CUDA(ctx, mark(4));
