@@ -434,6 +434,7 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "slots_per_pixel") ctx->opt_slots_per_pixel = value;
     else if (n == "tail_threshold") ctx->opt_tail_threshold = value;
     else if (n == "dense") ctx->opt_dense = value;
+    else if (n == "shade_sort") ctx->opt_shade_sort = value;
     else if (n == "dense_threshold") ctx->opt_dense_threshold = value;
     else if (n == "nee_refill_below") ctx->opt_nee_refill_below = value < 1 ? 1 : (value > 32 ? 32 : value);
     else if (n == "refill_below") ctx->opt_refill_below = value < 1 ? 1 : (value > 32 ? 32 : value);

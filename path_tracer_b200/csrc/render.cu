@@ -208,7 +208,7 @@ struct ExtendJob
             if (tr.hit_inst == TRAV_NONE)
             {
                 V.hit[slot].info = 0xffffffffu;
-                kind = Q_MISS;
+                V.hit[slot].kind = kind = Q_MISS;
             }
             else
             {
@@ -218,7 +218,7 @@ struct ExtendJob
                 finish_hit(V.S, tr.dw, tr.hit_inst, prim, wide_hit_u(tr), wide_hit_v(tr), &n, &ff);
                 V.hit[slot].tn = f4(tr.t_max, n.x, n.y, n.z);
                 V.hit[slot].info = tr.hit_inst | (ff ? 0x80000000u : 0u);
-                kind = V.S.mat[V.S.inst[tr.hit_inst].blas].kind;
+                V.hit[slot].kind = kind = V.S.mat[V.S.inst[tr.hit_inst].blas].kind;
             }
             if (sort == 0) kind = 0u;
         }
@@ -444,6 +444,7 @@ __global__ void __launch_bounds__(128) k_nee_bin(RenderView V, Queues Q, uint32_
 // iteration (set by the previous shade or by k_extend's regeneration), so that the walk knows which lanes of a group have a hit
 // record.  The host may switch between the two shade kernels at any iteration: both leave valid cont / term / nee queues.
 constexpr uint32_t SHADE_ROWS = 8, SHADE_GROUPS = SHADE_ROWS * 8;
+template <bool SORT>
 __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q, uint32_t it)
 {
     WfSet& S = Q.c->set[it % 3u];
@@ -456,24 +457,109 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
     // per list and (row, warp): entries of that warp-row; after the scan: exclusive prefix within the span
     __shared__ uint32_t cnt[4][SHADE_GROUPS];
     __shared__ uint32_t base[4], live_total;
+    // span-local sort of the live slots by shade kind (7 kinds): counts per (kind, row, warp) -> offsets; the sorted slot numbers
+    __shared__ uint32_t kcnt[7][SHADE_GROUPS], kbase[8];
+    __shared__ uint32_t sorted[SHADE_GROUPS * 32u];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) live_total = 0u;
     __syncthreads();
-    uint32_t n_live = 0;
     for (uint32_t first = blockIdx.x * SHADE_GROUPS; first < n_grp; first += gridDim.x * SHADE_GROUPS)
     {
+        if constexpr (SORT)
+        {
+            // (1) classify: one warp per listed group, lanes = its 32 slots
+            uint32_t my_kind[SHADE_ROWS];
+    #pragma unroll
+            for (uint32_t row = 0; row < SHADE_ROWS; ++row)
+            {
+                const uint32_t gi = first + row * 8u + warp;
+                const uint32_t slot = gi < n_grp ? grp[gi] * 32u + lane : 0xffffffffu;
+                uint32_t kind = 7u;  // not live
+                if (slot < Q.npix && (Q.state[slot] & WF_NEXT)) kind = min(V.hit[slot].kind, 6u);
+                my_kind[row] = kind;
+    #pragma unroll
+                for (uint32_t k = 0; k < 7u; ++k)
+                {
+                    const unsigned m = __ballot_sync(0xffffffffu, kind == k);
+                    if (lane == k) kcnt[k][row * 8u + warp] = (uint32_t)__popc(m);
+                }
+            }
+            __syncthreads();
+            // (2) offsets: warp k scans the 64 counts of kind k; then the seven totals are chained
+            if (warp < 7u)
+            {
+                uint32_t* c = kcnt[warp];
+                const uint32_t a = c[2u * lane], b = c[2u * lane + 1u];
+                uint32_t incl = a + b;
+    #pragma unroll
+                for (int o = 1; o < 32; o <<= 1)
+                {
+                    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                    if ((int)lane >= o) incl += t;
+                }
+                const uint32_t excl = incl - (a + b);
+                c[2u * lane] = excl;
+                c[2u * lane + 1u] = excl + a;
+                if (lane == 31u) kbase[warp + 1u] = incl;
+            }
+            __syncthreads();
+            if (threadIdx.x == 0)
+            {
+                kbase[0] = 0u;
+                for (int k = 1; k <= 7; ++k) kbase[k] += kbase[k - 1];
+            }
+            __syncthreads();
+            // (3) scatter the slot numbers in kind order (ascending slot order within a kind)
+    #pragma unroll
+            for (uint32_t row = 0; row < SHADE_ROWS; ++row)
+            {
+                const uint32_t kind = my_kind[row];
+                const unsigned m = __match_any_sync(0xffffffffu, kind);
+                if (kind < 7u)
+                {
+                    const uint32_t gi = first + row * 8u + warp;
+                    sorted[kbase[kind] + kcnt[kind][row * 8u + warp] + (uint32_t)__popc(m & ((1u << lane) - 1u))] = grp[gi] * 32u + lane;
+                }
+            }
+            __syncthreads();
+            // (4) shade: consecutive threads take consecutive sorted entries, so a warp shades one kind (but for the few warps on a boundary)
+            const uint32_t span_live = kbase[7];
+    #pragma unroll 1
+            for (uint32_t i = threadIdx.x; i < span_live; i += 256u)
+            {
+                const uint32_t slot = sorted[i];
+                Q.state[slot] = shade_slot(V, slot);
+            }
+            if (threadIdx.x == 0) live_total += span_live;
+            __syncthreads();
+        }
+        else
+        {
+            // all kinds alike (one surface material in the scene): shade in place, one warp per listed group
+            uint32_t n_live = 0;
+#pragma unroll 1
+            for (uint32_t row = 0; row < SHADE_ROWS; ++row)
+            {
+                const uint32_t gi = first + row * 8u + warp;
+                const uint32_t slot = gi < n_grp ? grp[gi] * 32u + lane : 0xffffffffu;
+                if (slot < Q.npix && (Q.state[slot] & WF_NEXT))
+                {
+                    Q.state[slot] = shade_slot(V, slot);
+                    ++n_live;
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) n_live += __shfl_xor_sync(0xffffffffu, n_live, o);
+            if (lane == 0u && n_live) atomicAdd(&live_total, n_live);
+        }
+        // (5) back in slot order: the four ascending output lists
 #pragma unroll 1
         for (uint32_t row = 0; row < SHADE_ROWS; ++row)
         {
             const uint32_t gi = first + row * 8u + warp;
             const uint32_t slot = gi < n_grp ? grp[gi] * 32u + lane : 0xffffffffu;
-            uint32_t flags = 0u;
-            if (slot < Q.npix && (Q.state[slot] & WF_NEXT))
-            {
-                flags = shade_slot(V, slot);
-                ++n_live;
-            }
-            if (slot < Q.npix) Q.state[slot] = flags;
+            // every non-zero flag word of a listed group now is this pass's: the pass ran on the WF_NEXT slots and the others were 0
+            const uint32_t flags = slot < Q.npix ? Q.state[slot] : 0u;
             const unsigned mt = __ballot_sync(0xffffffffu, (flags & WF_TERM) != 0u), mc = __ballot_sync(0xffffffffu, (flags & WF_NEXT) != 0u);
             const unsigned mn = __ballot_sync(0xffffffffu, (flags & (WF_SHADOW | WF_PROBE)) != 0u);
             if (lane == 0u)
@@ -518,10 +604,6 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
         }
         __syncthreads();
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) n_live += __shfl_xor_sync(0xffffffffu, n_live, o);
-    if (lane == 0u && n_live) atomicAdd(&live_total, n_live);
-    __syncthreads();
     if (threadIdx.x == 0 && live_total) atomicAdd(&Q.c->stat_extend, (unsigned long long)live_total);
 }
 
@@ -891,6 +973,14 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     bool dense = !bin && ctx->opt_dense != 0;
     const uint64_t dense_pct = (uint64_t)std::max(0, std::min(100, ctx->opt_dense_threshold));
     const int shade_grid = ctx->sm_count * 8;
+    // span-local sort by shade kind: worth its extra passes when warps would otherwise mix surface materials (auto: >= 2 non-emissive kinds)
+    bool shade_sort = ctx->opt_shade_sort > 0;
+    if (ctx->opt_shade_sort < 0)
+    {
+        uint32_t kinds = 0;
+        for (const auto& b : ctx->scene.blas_desc) kinds |= 1u << std::min<uint32_t>(b.material.kind, 7u);
+        shade_sort = __builtin_popcount(kinds & ~2u) >= 2;  // kind 1 = Emissive
+    }
     for (uint32_t it = 0;; ++it)
     {
         const int rb = ctx->opt_refill_below, rbn = ctx->opt_nee_refill_below, nq = ctx->opt_node_quorum;
@@ -907,7 +997,8 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             }
         }
         PTB_CUDA(ctx, mark(2));
-        if (dense) k_shade_ordered<<<shade_grid, 256, 0, st>>>(V, Q, it);
+        if (dense && shade_sort) k_shade_ordered<true><<<shade_grid, 256, 0, st>>>(V, Q, it);
+        else if (dense) k_shade_ordered<false><<<shade_grid, 256, 0, st>>>(V, Q, it);
         else k_shade<<<grid, threads, 0, st>>>(V, Q, it);
         PTB_CUDA(ctx, mark(3));
         rs.launches += 2;

@@ -38,7 +38,7 @@ struct alignas(32) HitRec     // HitInfo (model.rs:5-11) as the shade stage need
     float4 tn;        // t, world-space ray-facing normal.xyz
     uint32_t info;    // InstanceRow index | front_facing << 31 ; 0xffffffff = miss
     uint32_t rng_lo, rng_hi;
-    uint32_t pad;
+    uint32_t kind;    // shade kind of this hit (material kind 0..5, Q_MISS), written by k_extend for k_shade_ordered's span-local sort
 };
 struct alignas(32) ShadowRec  // explicit light sample awaiting its visibility test (integrator.rs:56)
 {
