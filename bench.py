@@ -229,7 +229,7 @@ def main():
                     peak_source=peak_src, alg_bytes_per_ray=alg_ext, rays_per_launch=cn["extend"] / max(ext_launches, 1), launch_ms=ext_ms / max(ext_launches, 1),
                     grays_per_s=cn["extend"] / (ext_ms * 1e-3) / 1e9,
                     note="achieved = algorithmic bytes of the REFERENCE traversal (oracle-counted slab/triangle/instance work on its binary BVH) per second of k_extend time, not DRAM traffic: "
-                         + ("the BVH of this workload is L1/L2-resident; " if args.workload != "c4" else "") + "ncu shows k_extend issue-bound (64 % issue slots active, 14/32 lanes per instruction), see DESIGN.md §5 and profiles/",
+                         + ("the BVH of this workload is L1/L2-resident; " if args.workload != "c4" else "") + "ncu shows k_extend issue-bound (64-70 % issue slots active, 14-15/32 lanes per instruction), see DESIGN.md §5 and profiles/",
                     stage_ms={k: round(v[0] / args.steps, 3) for k, v in tm.items()},
                     shadow=dict(alg_bytes_per_ray=alg_sha, achieved=(cn["shadow"] * alg_sha / (tm["nee"][0] * 1e-3) / 1e9) if tm["nee"][0] > 0 else None,
                                 note="k_nee also traces the light probes (lights-TLAS closest hit), not counted here"))
@@ -241,7 +241,7 @@ def main():
                 higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
                 config=dict(workload=WORKLOADS[args.workload]["desc"], width=W, height=H, spp_per_step_per_gpu=spp, max_bounces=sd.max_bounces, nee=True,
                             partition="disjoint global sample ranges per GPU, one NCCL reduce of the accumulation buffer per step" if world > 1 else "single GPU",
-                            l2="per-step working set (path state: 4 slots/pixel x 160 B + queues = %.0f MB) exceeds L2 (126 MB); no flush needed" % (W * H * 4 * 208 / 1e6), build_seconds=round(build_s, 2),
+                            l2="per-step working set (path state: 8 slots/pixel x 196 B + queues = %.0f MB) exceeds L2 (126 MB); no flush needed" % (W * H * 8 * 248 / 1e6), build_seconds=round(build_s, 2),
                             device_ms_per_step=dev_ms / args.steps),
                 e2e=dict(value=e2e_value, unit="Mrays/s", h2d_bytes_per_step=76 + 24, d2h_bytes_per_step=W * H * 36, ms_per_step=el_e / args.steps * 1e3),
                 gpu_launches=int(rays[2]), clocks=sampler.summary(), rays=dict(world=rays[0], light_probes=rays[1], paths=rays[3]))
