@@ -1010,6 +1010,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
                 const int g = ctx->sm_count * ctx->opt_nee_blocks;
                 switch (ctx->opt_nee_blocks)
                 {
+                case 4: k_nee<4><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
                 case 7: k_nee<7><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
                 case 8: k_nee<8><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
                 case 6: k_nee<6><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
