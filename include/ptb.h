@@ -201,14 +201,24 @@ int ptb_get_counters(ptb_context* ctx, uint64_t out[8]);
 int ptb_reset_counters(ptb_context* ctx);
 /* With profiling on, every kernel launch of ptb_render is bracketed by CUDA events on the context stream.
  * times_ms: [0] whole ptb_render call (always measured), [1] init, [2] extend (incl. finalise/accumulate/raygen of regenerated
- * slots), [3] shade, [4] nee (shadow + light-probe rays), [5] tail (all stages, one launch), [6..7] reserved; launches: same indices. */
+ * slots), [3] shade, [4] nee (shadow + light-probe rays), [5] tail (all stages, one launch), [6] combine, [7] reserved; launches: same indices. */
 int ptb_set_profiling(ptb_context* ctx, int enable);
 int ptb_get_timing(ptb_context* ctx, float times_ms[8], uint32_t launches[8]);
 /* Active slots (paths in flight + slots awaiting regeneration) after each wavefront iteration of the last ptb_render (first 8192). */
 int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active, uint32_t* count);
-/* Tunables (evidence switches for DESIGN.md's layout decisions): name in {"sort_materials","extend_kernel","block_threads",
- * "blocks_per_sm","tail_threshold"}.  tail_threshold: active slots at which the wavefront loop hands the remaining slots to the
- * single-launch tail kernel (< 0 automatic = half the resident thread capacity of that kernel, 0 = never). */
+/* Tunables (evidence switches for DESIGN.md's layout decisions), name = value:
+ *   extend_kernel     0 the 8-wide persistent kernels (default), 1 the reference-order kernels over the reference's binary trees
+ *   slots_per_pixel   path slots per pixel, 1..16 (default 8)
+ *   dense             1 k_shade_ordered (slot-ordered shading, ascending queues; default), 0 the queue shade kernel throughout
+ *   dense_threshold   live slots per listed 32-slot group, in percent, below which the queue shade kernel takes over (default 60)
+ *   shade_sort        span-local sort by shade kind in k_shade_ordered: 1, 0, < 0 automatic (scenes with >= 2 surface material kinds)
+ *   sort_materials    queue shade kernel: one queue per material kind (default 1)
+ *   extend_blocks, nee_blocks   resident blocks per SM (= register cap) of k_extend (5..8, default 6) / k_nee (4..8, default 5)
+ *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit 8, any-hit 16)
+ *   node_quorum       lanes that must want the node stage before it runs (default 8)
+ *   tail_threshold    active slots at which the wavefront loop hands the remaining slots to the single-launch tail kernel
+ *                     (< 0 automatic = half the resident thread capacity of that kernel, 0 = never)
+ *   block_threads, blocks_per_sm     launch shape of the queue shade / reference-order kernels */
 int ptb_set_option(ptb_context* ctx, const char* name, int value);
 
 #ifdef __cplusplus
