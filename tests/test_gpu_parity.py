@@ -268,20 +268,20 @@ def test_env_map_render_same_streams(ptb, po, scenes, tmp_path):
     assert (rel > 1e-3).mean() < 0.01
 
 
-@pytest.mark.parametrize("name,spp", [("c2", 6), ("c3_small", 5), ("materials", 4)])
-def test_slot_ordered_and_queue_kernels_agree(ptb, scenes, name, spp):
+@pytest.mark.parametrize("name,spp,W,H", [("c2", 6, 96, 54), ("c3_small", 5, 96, 54), ("materials", 4, 96, 54), ("c2", 7, 97, 53), ("materials", 19, 33, 21)])
+def test_slot_ordered_and_queue_kernels_agree(ptb, scenes, name, spp, W, H):
     """The slot-ordered kernels (k_extend_dense / k_shade_dense / k_nee_dense) and the queue kernels run the same per-slot bodies on the
     same per-slot RNG streams, whichever mix of the two the host loop uses (switch-over at 100 %, 50 %, 10 % live slots, or never).
     Exact tier (first-hit position, ids, ray counts): identical.  Radiance: the shading arithmetic is ordinary float code that the
     compiler may contract differently in the two kernels, so sums agree to rounding (1e-5 relative), not bit for bit."""
     sd = _scene(scenes, name)
-    W, H = 96, 54
-    out = {}
+    out = {}  # 97x53x7 and 33x21x8 slots: not multiples of 32 (ragged last group) nor of the 2048-slot span
     for dense, thr in ((0, 0), (1, 0), (1, 10), (1, 50), (1, 100)):
         ctx = ptb.Context(0)
         ctx.upload(sd)
         ctx.set_option("dense", dense)
         ctx.set_option("dense_threshold", thr)
+        ctx.set_option("shade_sort", 1 if thr == 50 else -1)  # one schedule with the span-local sort forced on
         ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
         ctx.frame_begin(W, H)
         ctx.reset_counters()
