@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(256) k_accumulate(const float4* __restrict__ i
 }
 
 // 32 x 8 pixel blocks: a warp covers 32 consecutive texels of a row (512 B of each rgba32float image per load)
-__global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ input, const float4* __restrict__ history, const float4* __restrict__ position,
+__global__ void __launch_bounds__(256, 4) k_resolve(const float4* __restrict__ input, const float4* __restrict__ history, const float4* __restrict__ position,
                                                  const uint32_t* __restrict__ id, Mat4Arg last, int W, int H, int input_is_sum, float4* __restrict__ out, float2* __restrict__ velocity)
 {
     const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
