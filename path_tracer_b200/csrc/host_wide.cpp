@@ -357,6 +357,13 @@ SceneDev host_view(const HostScene& sc)
         S.tlas[w].bin_root = sc.tlas[w].root;
         S.tlas[w].inst_base = sc.tlas[w].inst_base;
         S.tlas[w].inst_count = (uint32_t)(w == 0 ? (sc.tlas[1].inst_base - sc.tlas[0].inst_base) : (sc.inst_rows.size() - sc.tlas[1].inst_base));
+        const HostTlasNode& rn = sc.tlas[w].nodes[sc.tlas[w].root];
+        for (int k = 0; k < 3; ++k)
+        {
+            const float m = 1e-4f * ((rn.hi[k] - rn.lo[k]) + std::fabs(rn.lo[k]) + std::fabs(rn.hi[k]) + 1.0f);
+            S.tlas[w].box_lo[k] = rn.lo[k] - m;
+            S.tlas[w].box_hi[k] = rn.hi[k] + m;
+        }
     }
     S.n_lights = (uint32_t)sc.light_rows.size();
     S.n_volumes = (uint32_t)sc.volumes.size();

@@ -116,7 +116,10 @@ struct TlasDev
     uint32_t bin_root;    // TLAS-local
     uint32_t inst_base;   // first InstanceRow of this TLAS
     uint32_t inst_count;
-    uint32_t pad[3];
+    // world bounds of everything under this TLAS, widened by a rounding margin (host_wide.cpp): a ray that misses them
+    // under an approximate slab test cannot hit any of its triangles (tlas_may_hit, traverse.h)
+    float box_lo[3], box_hi[3];
+    uint32_t pad;
 };
 
 // Everything the kernels need, passed by value

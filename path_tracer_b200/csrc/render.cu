@@ -332,12 +332,16 @@ struct NeeJob
     uint32_t lslot = 0, linst = 0;
     unsigned long long n_shadow = 0, n_probe = 0, n_probe_shadow = 0;
 
-    __device__ __forceinline__ void begin_probe(WideTrav& tr)
+    // false: the probe direction cannot reach the bounds of the lights, nothing to trace (integrator.rs:100 returns None)
+    __device__ __forceinline__ bool begin_probe(WideTrav& tr)
     {
         const float4 d4 = V.probe[slot].d;
-        wide_begin(tr, V.S, 1, o, ex::v3(d4.x, d4.y, d4.z), ex::inf(), false);
-        stage = 1;
+        const V3 d = ex::v3(d4.x, d4.y, d4.z);
         ++n_probe;
+        if (!tlas_may_hit(V.S, 1, o, d)) return false;
+        wide_begin(tr, V.S, 1, o, d, ex::inf(), false);
+        stage = 1;
+        return true;
     }
     __device__ __forceinline__ bool begin_slot(uint32_t slot_, uint32_t flags_, WideTrav& tr)
     {
@@ -353,7 +357,7 @@ struct NeeJob
             stage = 0;
             ++n_shadow;
         }
-        else begin_probe(tr);
+        else return begin_probe(tr);
         return true;
     }
     __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
@@ -371,7 +375,7 @@ struct NeeJob
                 const float4 c = V.shadow[slot].c;
                 r.x += c.x; r.y += c.y; r.z += c.z;
             }
-            if (flags & WF_PROBE) { begin_probe(tr); return true; }
+            if ((flags & WF_PROBE) && begin_probe(tr)) return true;
         }
         else if (stage == 1)
         {

@@ -197,6 +197,30 @@ struct WideTrav
     uint32_t any;       // any-hit query (TLAS::any_intersect) — used when the step is instantiated with MODE == 2
 };
 
+// Conservative pre-test against the widened world bounds of TLAS `which`: false only if no point of the ray (t >= 0) lies in
+// them, so no triangle of that TLAS can be hit.  Approximate reciprocals are enough (the margin absorbs the rounding); an
+// axis with a (nearly) zero direction component constrains nothing.  Used for the BSDF-sampled light probes, most of which
+// point nowhere near the lights: they end here instead of after a ray set-up and a node test.
+PTB_HD bool tlas_may_hit(const SceneDev& S, int which, V3 o, V3 d)
+{
+    const TlasDev& T = S.tlas[which];
+    float tn = 0.0f, tf = ex::inf();
+    const float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        if (fabsf(dd[k]) > 1e-30f)
+        {
+#if defined(__CUDA_ARCH__)
+            const float inv = __fdividef(1.0f, dd[k]);
+#else
+            const float inv = 1.0f / dd[k];
+#endif
+            const float t0 = (T.box_lo[k] - oo[k]) * inv, t1 = (T.box_hi[k] - oo[k]) * inv;
+            tn = fmaxf(tn, fminf(t0, t1));
+            tf = fminf(tf, fmaxf(t0, t1));
+        }
+    return tn <= tf * 1.00001f + 1e-30f;
+}
 PTB_HD float wide_hit_u(const WideTrav& s) { return ex::div(s.hit_ud, s.hit_det); }
 PTB_HD float wide_hit_v(const WideTrav& s) { return ex::div(s.hit_vd, s.hit_det); }
 PTB_HD void wide_begin(WideTrav& s, const SceneDev& S, int which, V3 o, V3 d, float t_max, bool any)

@@ -406,6 +406,7 @@ PTB_HD uint32_t probe_contrib_t(const RenderView& V, uint32_t slot, V3 o, float4
 {
     const float4 d4 = V.probe[slot].d;
     const V3 d = ex::v3(d4.x, d4.y, d4.z);
+    if (!BIN && !tlas_may_hit(V.S, 1, o, d)) return 0u;  // cannot reach the bounds of the lights (the reference-order variant always traverses)
     Hit h;
     h.inst = 0xffffffffu;
     const bool lit = BIN ? bin_traverse<false>(V.S, 1, o, d, ex::inf(), &h) : wide_traverse<false>(V.S, 1, o, d, ex::inf(), &h);  // integrator.rs:100
