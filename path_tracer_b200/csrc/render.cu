@@ -313,6 +313,8 @@ __global__ void __launch_bounds__(128) k_shade(RenderView V, Queues Q, uint32_t 
         warp_push(Q.nee, &S.n_nee, (flags & (WF_SHADOW | WF_PROBE)) != 0u, slot | ((flags & WF_SHADOW) ? NEE_SHADOW_BIT : 0u) | ((flags & WF_PROBE) ? NEE_PROBE_BIT : 0u));
         warp_push(Q.cont[nb], &N.n_cont, (flags & WF_NEXT) != 0u, slot);
         warp_push(Q.term[nb], &N.n_term, (flags & WF_TERM) != 0u, slot);
+        const unsigned mo = __ballot_sync(0xffffffffu, (flags & WF_PROBE_OUT) != 0u);
+        if (lane == 0u && mo) atomicAdd(&Q.c->stat_probe, (unsigned long long)__popc(mo));
     }
 }
 
@@ -460,12 +462,13 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
     const uint32_t n_grp = S.n_grp;
     // per list and (row, warp): entries of that warp-row; after the scan: exclusive prefix within the span
     __shared__ uint32_t cnt[4][SHADE_GROUPS];
-    __shared__ uint32_t base[4], live_total;
+    __shared__ uint32_t base[4], live_total, out_total;
+    uint32_t n_out = 0;  // probes settled by the bounds pre-test in shade_slot (statistics)
     // span-local sort of the live slots by shade kind (7 kinds): counts per (kind, row, warp) -> offsets; the sorted slot numbers
     __shared__ uint32_t kcnt[7][SHADE_GROUPS], kbase[8];
     __shared__ uint32_t sorted[SHADE_GROUPS * 32u];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) live_total = 0u;
+    if (threadIdx.x == 0) { live_total = 0u; out_total = 0u; }
     __syncthreads();
     for (uint32_t first = blockIdx.x * SHADE_GROUPS; first < n_grp; first += gridDim.x * SHADE_GROUPS)
     {
@@ -532,7 +535,9 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
             for (uint32_t i = threadIdx.x; i < span_live; i += 256u)
             {
                 const uint32_t slot = sorted[i];
-                Q.state[slot] = shade_slot(V, slot);
+                const uint32_t flags = shade_slot(V, slot);
+                Q.state[slot] = flags;
+                n_out += (flags & WF_PROBE_OUT) ? 1u : 0u;
             }
             if (threadIdx.x == 0) live_total += span_live;
             __syncthreads();
@@ -548,7 +553,9 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
                 const uint32_t slot = gi < n_grp ? grp[gi] * 32u + lane : 0xffffffffu;
                 if (slot < Q.npix && (Q.state[slot] & WF_NEXT))
                 {
-                    Q.state[slot] = shade_slot(V, slot);
+                    const uint32_t flags = shade_slot(V, slot);
+                    Q.state[slot] = flags;
+                    n_out += (flags & WF_PROBE_OUT) ? 1u : 0u;
                     ++n_live;
                 }
             }
@@ -608,7 +615,12 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
         }
         __syncthreads();
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n_out += __shfl_xor_sync(0xffffffffu, n_out, o);
+    if (lane == 0u && n_out) atomicAdd(&out_total, n_out);
+    __syncthreads();
     if (threadIdx.x == 0 && live_total) atomicAdd(&Q.c->stat_extend, (unsigned long long)live_total);
+    if (threadIdx.x == 0 && out_total) atomicAdd(&Q.c->stat_probe, (unsigned long long)out_total);
 }
 
 // The tail: one thread per remaining slot runs regen -> extend -> shade -> shadow -> probe until the slot has no samples left.
@@ -641,6 +653,7 @@ __global__ void __launch_bounds__(64) k_tail(RenderView V, Queues Q, uint32_t it
             extend_ray_t<BIN>(V, slot, o, d);
             ++n_ext;
             const uint32_t flags = shade_slot(V, slot);
+            n_pr += (flags & WF_PROBE_OUT) ? 1u : 0u;
             if (flags & (WF_SHADOW | WF_PROBE))
             {
                 n_ps += nee_slot_t<BIN>(V, slot, flags);

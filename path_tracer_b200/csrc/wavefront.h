@@ -77,7 +77,8 @@ struct RenderView
     unsigned long long* volset;
 };
 
-enum : uint32_t { WF_NEXT = 1u, WF_TERM = 2u, WF_SHADOW = 4u, WF_PROBE = 8u };
+enum : uint32_t { WF_NEXT = 1u, WF_TERM = 2u, WF_SHADOW = 4u, WF_PROBE = 8u,
+                  WF_PROBE_OUT = 16u };  // a BSDF-sampled light direction that cannot reach the bounds of the lights: counted as a probe, nothing to trace
 constexpr uint32_t ST_LAST_DELTA = 1u << 24, ST_HAS_SAMPLE = 1u << 25, ST_BOUNCE_MASK = (1u << 24) - 1u;
 constexpr uint32_t NEE_SHADOW_BIT = 0x80000000u, NEE_PROBE_BIT = 0x40000000u, NEE_SLOT_MASK = 0x3fffffffu;  // nee queue entry = slot | flags
 constexpr uint32_t Q_MISS = 6;  // shade queue kinds: 0..5 = material kinds, 6 = miss
@@ -319,10 +320,14 @@ PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
                     const BsdfPdf bp = bsdf_pdf(mat, wi, pd, normal, front);
                     if (bp.pdf > 0.0f)  // MIN_PDF (checked upstream after the visibility tests; order is immaterial)
                     {
-                        const V3 f = path_weight * (weakening(mat.kind, pd, normal) * bp.bsdf / bp.pdf);
-                        V.probe[slot].d = f4(pd.x, pd.y, pd.z, bp.pdf);
-                        V.probe[slot].f = f4(f.x, f.y, f.z, 0.0f);
-                        flags |= WF_PROBE;
+                        if (!V.extend_kernel && !tlas_may_hit(V.S, 1, hit_p, pd)) flags |= WF_PROBE_OUT;  // integrator.rs:100 would return None
+                        else
+                        {
+                            const V3 f = path_weight * (weakening(mat.kind, pd, normal) * bp.bsdf / bp.pdf);
+                            V.probe[slot].d = f4(pd.x, pd.y, pd.z, bp.pdf);
+                            V.probe[slot].f = f4(f.x, f.y, f.z, 0.0f);
+                            flags |= WF_PROBE;
+                        }
                     }
                 }
             }

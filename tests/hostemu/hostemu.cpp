@@ -148,6 +148,7 @@ void emu_render(void* h, const float* cam_m16, const float* cam_eye3, uint32_t W
             for (uint32_t s : mat[k])
             {
                 const uint32_t f = shade_slot(V, s);
+                n_probe += (f & WF_PROBE_OUT) ? 1 : 0;
                 if (f & (WF_SHADOW | WF_PROBE)) nee.push_back(s | ((f & WF_SHADOW) ? NEE_SHADOW_BIT : 0u) | ((f & WF_PROBE) ? NEE_PROBE_BIT : 0u));
                 if (f & WF_NEXT) next.push_back(s);
                 if (f & WF_TERM) term.push_back(s);
