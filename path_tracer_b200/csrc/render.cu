@@ -196,6 +196,14 @@ struct ExtendJob
             Q.state[slot] = f;  // live (a ray is being traced for it this iteration) or out of samples
             if (!f) return false;
             ++paths;
+            // a camera outside the scene bounds: primary rays that cannot reach them are misses without a traversal (slot-ordered
+            // shading only: the queue shade kernel expects the slot in its miss queue, pushed by finish())
+            if (sort < 0 && !tlas_may_hit(V.S, 0, o, d))
+            {
+                V.hit[slot].info = 0xffffffffu;
+                V.hit[slot].kind = Q_MISS;
+                return false;
+            }
         }
         wide_begin(tr, V.S, 0, o, d, ex::inf(), false);
         return true;
