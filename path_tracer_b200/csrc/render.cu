@@ -177,7 +177,7 @@ struct ExtendJob
     uint32_t b, n_cont, n_term;
     int sort;  // 1: push the slot to the shade queue of its material kind, 0: to queue 0, -1: no push (k_shade_ordered walks the slots itself)
     uint32_t slot = 0;
-    unsigned long long paths = 0;
+    unsigned long long paths = 0, settled = 0;
 
     __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
     {
@@ -192,18 +192,20 @@ struct ExtendJob
         else
         {
             slot = Q.term[b][idx - n_cont];
-            const uint32_t f = regen_slot(V, slot, &o, &d) & WF_NEXT;
-            Q.state[slot] = f;  // live (a ray is being traced for it this iteration) or out of samples
-            if (!f) return false;
-            ++paths;
-            // a camera outside the scene bounds: primary rays that cannot reach them are misses without a traversal (slot-ordered
-            // shading only: the queue shade kernel expects the slot in its miss queue, pushed by finish())
-            if (sort < 0 && !tlas_may_hit(V.S, 0, o, d))
+            for (;;)
             {
-                V.hit[slot].info = 0xffffffffu;
-                V.hit[slot].kind = Q_MISS;
-                return false;
+                const uint32_t f = regen_slot(V, slot, &o, &d) & WF_NEXT;
+                if (!f) { Q.state[slot] = 0u; return false; }  // out of samples
+                ++paths;
+                // A camera outside the scene bounds: a primary ray that cannot reach them is a miss without a traversal, and with the
+                // constant background the whole path is that miss (integrator.rs:254-269 at b == 0: radiance = background * 1).  Settle
+                // it here and start the slot's next sample at once; background pixels then never occupy the later kernels.
+                // (Slot-ordered shading only: the queue shade kernel expects every traced slot in one of its queues.)
+                if (sort >= 0 || V.S.env != nullptr || tlas_may_hit(V.S, 0, o, d)) break;
+                V.path[slot].radiance = f4(0.006f, 0.006f, 0.006f, 0.0f);
+                ++settled;
             }
+            Q.state[slot] = WF_NEXT;  // live: a ray is being traced for it this iteration
         }
         wide_begin(tr, V.S, 0, o, d, ex::inf(), false);
         return true;
@@ -247,8 +249,9 @@ __global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint
     }
     ExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort};
     persistent_trace<0>(V.S, job, &S.cur_extend, n_cont + n_term, refill_below, node_quorum);
-    const unsigned long long p = warp_sum(job.paths);
+    const unsigned long long p = warp_sum(job.paths), q = warp_sum(job.settled);
     if ((threadIdx.x & 31u) == 0u && p) atomicAdd(&Q.c->stat_paths, p);
+    if ((threadIdx.x & 31u) == 0u && q) atomicAdd(&Q.c->stat_extend, q);  // primary rays settled in start(): rays nonetheless
 }
 
 // reference-order variant (binary trees, reference visit order): static chunks of 32, one ray per lane
