@@ -241,7 +241,7 @@ def main():
                 higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
                 config=dict(workload=WORKLOADS[args.workload]["desc"], width=W, height=H, spp_per_step_per_gpu=spp, max_bounces=sd.max_bounces, nee=True,
                             partition="disjoint global sample ranges per GPU, one NCCL reduce of the accumulation buffer per step" if world > 1 else "single GPU",
-                            l2="per-step working set (path state: 8 slots/pixel x 196 B + queues = %.0f MB) exceeds L2 (126 MB); no flush needed" % (W * H * 8 * 248 / 1e6), build_seconds=round(build_s, 2),
+                            l2="per-step working set (path state: 16 slots/pixel x 196 B + queues = %.0f MB) exceeds L2 (126 MB); no flush needed" % (W * H * 16 * 248 / 1e6), build_seconds=round(build_s, 2),
                             device_ms_per_step=dev_ms / args.steps),
                 e2e=dict(value=e2e_value, unit="Mrays/s", h2d_bytes_per_step=76 + 24, d2h_bytes_per_step=W * H * 36, ms_per_step=el_e / args.steps * 1e3),
                 gpu_launches=int(rays[2]), clocks=sampler.summary(), rays=dict(world=rays[0], light_probes=rays[1], paths=rays[3]))

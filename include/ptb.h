@@ -208,13 +208,13 @@ int ptb_get_timing(ptb_context* ctx, float times_ms[8], uint32_t launches[8]);
 int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active, uint32_t* count);
 /* Tunables (evidence switches for DESIGN.md's layout decisions), name = value:
  *   extend_kernel     0 the 8-wide persistent kernels (default), 1 the reference-order kernels over the reference's binary trees
- *   slots_per_pixel   path slots per pixel, 1..16 (default 8)
+ *   slots_per_pixel   path slots per pixel, 1..16 (default 16)
  *   dense             1 k_shade_ordered (slot-ordered shading, ascending queues; default), 0 the queue shade kernel throughout
  *   dense_threshold   live slots per listed 32-slot group, in percent, below which the queue shade kernel takes over (default 60)
  *   shade_sort        span-local sort by shade kind in k_shade_ordered: 1, 0, < 0 automatic (scenes with >= 2 surface material kinds)
  *   sort_materials    queue shade kernel: one queue per material kind (default 1)
  *   extend_blocks, nee_blocks   resident blocks per SM (= register cap) of k_extend (5..8, default 6) / k_nee (4..8, default 5)
- *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit 8, any-hit 16)
+ *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit 8, any-hit 12)
  *   node_quorum       lanes that must want the node stage before it runs (default 8)
  *   tail_threshold    active slots at which the wavefront loop hands the remaining slots to the single-launch tail kernel
  *                     (< 0 automatic = half the resident thread capacity of that kernel, 0 = never)
