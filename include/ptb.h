@@ -208,6 +208,7 @@ int ptb_get_timing(ptb_context* ctx, float times_ms[8], uint32_t launches[8]);
 int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active, uint32_t* count);
 /* Tunables (evidence switches for DESIGN.md's layout decisions), name = value:
  *   extend_kernel     0 the 8-wide persistent kernels (default), 1 the reference-order kernels over the reference's binary trees
+ *   wide_collapse     8-wide collapse of the reference trees at the next ptb_build: 1 least summed node area (default), 0 greedy
  *   slots_per_pixel   path slots per pixel, 1..16 (default 16)
  *   dense             1 k_shade_ordered (slot-ordered shading, ascending queues; default), 0 the queue shade kernel throughout
  *   dense_threshold   live slots per listed 32-slot group, in percent, below which the queue shade kernel takes over (default 60)

@@ -57,6 +57,7 @@ struct HostScene
     std::vector<ptb_instance> instances;
     std::vector<float> env;
     uint32_t env_w = 0, env_h = 0;
+    int wide_collapse = 1;  // 8-wide collapse of the reference trees: 1 = minimum summed node area (dynamic programme), 0 = greedy largest-area-first
     // build products
     std::vector<HostTri> tris;  // global triangle order
     std::vector<HostBlas> blas;

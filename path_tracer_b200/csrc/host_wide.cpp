@@ -2,7 +2,7 @@
 // concatenated BinNode arrays for the reference-order kernel, and the 8-wide compressed nodes + exact leaf headers +
 // leaf-ordered triangle planes for the persistent kernels.
 //
-// Collapse: start from a binary node's two children and repeatedly open the branch child with the largest surface area
+// Collapse (wide_collapse = 0): start from a binary node's two children and repeatedly open the branch child with the largest surface area
 // until 8 children or only leaves remain (reference leaves are never split or merged: each keeps its exact AABB, H2).
 // Slots are assigned greedily so that slot index bits (x=4,y=2,z=1) follow the child's centroid offset; traversal
 // visits hit slots in descending (slot ^ (7 ^ octant)) order, which is front to back.  Child boxes are quantised to
@@ -76,6 +76,69 @@ struct Collapser
     uint32_t inst_base = 0;  // TLAS: first InstanceRow
     uint32_t max_depth = 0;
 
+    // Optimal collapse (after Ylitie, Karras, Laine 2017, section 3.1), specialised to fixed leaves: every reference leaf stays a leaf
+    // (its exact box is part of the parity contract), so the only freedom is WHICH binary branch nodes become 8-wide nodes, and the
+    // SAH cost to minimise is the summed surface area of those.  plan[n].cost[i-1] = least cost of representing the subtree of
+    // binary node n by at most i child slots of its parent; split[j-2] = how many of j slots go to the left child when n is dissolved.
+    struct Plan
+    {
+        float cost[7];     // [i-1]: least cost with at most i slots
+        uint8_t split[7];  // [j-2]: slots given to the left child when the node is dissolved into j slots
+        uint8_t used[7];   // [i-1]: slots actually taken at that optimum (1 = the node stays an 8-wide node of its own)
+    };
+    std::vector<Plan> plan;
+
+    void make_plan()
+    {
+        plan.assign(tv.count, Plan{});
+        for (uint32_t n = 0; n < tv.count; ++n)  // both trees store children before their parent
+        {
+            Plan& P = plan[n];
+            if (!tv.is_branch(tv.self, n)) { for (int i = 0; i < 7; ++i) { P.cost[i] = 0.0f; P.split[i] = 0; P.used[i] = 1; } continue; }
+            const Plan& L = plan[tv.left(tv.self, n)];
+            const Plan& R = plan[tv.right(tv.self, n)];
+            float dist[9];  // dist[j] = n dissolved into j >= 2 slots
+            for (int j = 2; j <= 8; ++j)
+            {
+                float best = 3.0e38f;
+                int bk = j / 2;
+                for (int t = 0; t < j; ++t)  // candidates from the balanced split outwards: ties (degenerate zero-area trees) stay balanced
+                {
+                    const int k = j / 2 + ((t & 1) ? (t + 1) / 2 : -(t / 2));
+                    if (k < 1 || k > j - 1 || k > 7 || j - k > 7) continue;
+                    const float c = L.cost[k - 1] + R.cost[j - k - 1];
+                    if (c < best) { best = c; bk = k; }
+                }
+                dist[j] = best;
+                if (j <= 8) P.split[j - 2] = (uint8_t)bk;
+            }
+            P.cost[0] = (float)box_sa(tv.lo(tv.self, n), tv.hi(tv.self, n)) + dist[8];  // n becomes a wide node of its own
+            P.used[0] = 1;
+            float best = P.cost[0];
+            uint8_t used = 1;
+            for (int i = 2; i <= 7; ++i)
+            {
+                if (dist[i] <= best) { best = dist[i]; used = (uint8_t)i; }  // on a tie rather dissolve: fewer, fuller nodes
+                P.cost[i - 1] = best;
+                P.used[i - 1] = used;
+            }
+        }
+    }
+    // children of the wide node rooted at binary node `bin` (budget slots): follow the plan
+    void gather(uint32_t bin, int budget, uint32_t* child, int& n)
+    {
+        const int k = plan[bin].split[budget - 2];
+        place(tv.left(tv.self, bin), k, child, n);
+        place(tv.right(tv.self, bin), budget - k, child, n);
+    }
+    void place(uint32_t bin, int budget, uint32_t* child, int& n)
+    {
+        if (!tv.is_branch(tv.self, bin)) { child[n++] = bin; return; }
+        const int j = plan[bin].used[budget - 1];
+        if (j == 1) { child[n++] = bin; return; }  // stays a node of its own
+        gather(bin, j, child, n);                   // dissolved into j slots
+    }
+
     void emit_leaf(uint32_t bin_id, bool root_leaf)
     {
         LeafHeader h{};
@@ -128,23 +191,28 @@ struct Collapser
             if (w.root_is_leaf) child[n++] = w.bin;
             else
             {
-                child[n++] = tv.left(tv.self, w.bin);
-                child[n++] = tv.right(tv.self, w.bin);
-                while (n < 8)
+                if (plan.empty())
                 {
-                    int best = -1;
-                    double best_sa = -1.0;
-                    for (int c = 0; c < n; ++c)
-                        if (tv.is_branch(tv.self, child[c]))
-                        {
-                            double s = box_sa(tv.lo(tv.self, child[c]), tv.hi(tv.self, child[c]));
-                            if (s > best_sa) { best_sa = s; best = c; }
-                        }
-                    if (best < 0) break;
-                    uint32_t b = child[best];
-                    child[best] = tv.left(tv.self, b);
-                    child[n++] = tv.right(tv.self, b);
+                    // greedy: open the branch child with the largest surface area until the node is full
+                    child[n++] = tv.left(tv.self, w.bin);
+                    child[n++] = tv.right(tv.self, w.bin);
+                    while (n < 8)
+                    {
+                        int best = -1;
+                        double best_sa = -1.0;
+                        for (int c = 0; c < n; ++c)
+                            if (tv.is_branch(tv.self, child[c]))
+                            {
+                                double s = box_sa(tv.lo(tv.self, child[c]), tv.hi(tv.self, child[c]));
+                                if (s > best_sa) { best_sa = s; best = c; }
+                            }
+                        if (best < 0) break;
+                        uint32_t b = child[best];
+                        child[best] = tv.left(tv.self, b);
+                        child[n++] = tv.right(tv.self, b);
+                    }
                 }
+                else gather(w.bin, 8, child, n);
             }
             // node box = box of the binary node (exact union of everything below)
             const float* nlo = tv.lo(tv.self, w.bin);
@@ -261,6 +329,7 @@ int collapse_scene(HostScene& sc, std::string& err)
         TreeView tv{B.nodes.size(), blas_lo, blas_hi, blas_branch, blas_left, blas_right, &B};
         Collapser c{sc, tv, false};
         c.blas = &B;
+        if (sc.wide_collapse) c.make_plan();
         B.wide_root = c.run(B.root);
         B.wide_depth = c.max_depth;
         max_blas_wide = std::max(max_blas_wide, B.wide_depth);
@@ -299,6 +368,7 @@ int collapse_scene(HostScene& sc, std::string& err)
         TreeView tv{T.nodes.size(), tlas_lo, tlas_hi, tlas_branch, tlas_left, tlas_right, &T};
         Collapser c{sc, tv, true};
         c.inst_base = T.inst_base;
+        if (sc.wide_collapse) c.make_plan();
         T.wide_root = c.run(T.root);
         T.wide_depth = c.max_depth;
         max_tlas_wide = std::max(max_tlas_wide, T.wide_depth);
