@@ -29,11 +29,15 @@ WORKLOADS = {
     "c2": dict(desc="synthetic Cornell box (36 tris, diffuse + area light) 1920x1080, 256 spp, max depth 8"),
     "c3": dict(desc="procedural 1M-triangle instanced scene (1K BLAS instances under a TLAS) 1920x1080, 64 spp"),
     "c4": dict(desc="procedural 10M-triangle displaced terrain + dielectric/glossy, 3840x2160, 16 spp, max depth 16 + RR"),
+    # BASELINE config 4: the frame's 4096 samples are split over the ranks (strong scaling); opt-in, a step is ~80 s / N on B200
+    "c5": dict(desc="4K 4096-spp sample-partitioned render of the 1M-triangle instanced scene, NCCL reduce of the accumulation buffers", strong=True),
 }
 
 
 def get_scene(name):
     from path_tracer_b200 import scenes
+    if name == "c5":
+        return scenes.scene_c3(width=3840, height=2160, spp=4096)
     return {"c2": scenes.scene_c2, "c3": scenes.scene_c3, "c4": scenes.scene_c4}[name]()
 
 
@@ -130,6 +134,8 @@ def main():
     sd = get_scene(args.workload)
     W, H = sd.width, sd.height
     spp = args.spp or sd.spp
+    strong = bool(WORKLOADS[args.workload].get("strong"))
+    per_step = spp if strong else world * spp  # global samples per step: fixed (strong) or spp per rank (weak)
     ctx = ptb.Context(local)  # raises without a GPU / without libptb.so: no fallback
     t0 = time.time()
     ctx.upload(sd)
@@ -151,9 +157,9 @@ def main():
         if e2e:
             ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, sd.aspect)  # the per-frame input of the seam (main.rs:199)
         ctx.frame_begin(W, H)  # clears the bound accumulation buffer
-        # weak scaling: step `index` covers the global samples [index*world*spp, +world*spp); rank r renders its block of spp,
-        # then ONE NCCL reduce of the accumulation buffer onto rank 0 (NVLink)
-        multi.render_partitioned(lambda first, n: ctx.render(first, n, seed=args.seed, max_bounces=sd.max_bounces), acc, index * world * spp, world * spp, rank, world)
+        # step `index` covers the global samples [index*per_step, +per_step); rank r renders its contiguous block of them (spp each
+        # under weak scaling, spp / world under strong), then ONE NCCL reduce of the accumulation buffer onto rank 0 (NVLink)
+        multi.render_partitioned(lambda first, n: ctx.render(first, n, seed=args.seed, max_bounces=sd.max_bounces), acc, index * per_step, per_step, rank, world)
         if world > 1:
             torch.cuda.synchronize()
         if e2e and rank == 0:
@@ -238,8 +244,8 @@ def main():
             roof["traffic"] = json.load(open(tr)).get(args.workload, {}).get("k_extend_dram_bytes_per_launch")
 
     line = dict(metric="Mrays/s (primary+shadow)", value=value, unit="Mrays/s", n_gpus=world, steps=args.steps, warmup=args.warmup, ms_per_step=el / args.steps * 1e3,
-                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload=WORKLOADS[args.workload]["desc"], width=W, height=H, spp_per_step_per_gpu=spp, max_bounces=sd.max_bounces, nee=True,
+                higher_is_better=True, scaling="strong" if strong else "weak", vs_baseline=None, dtype="f32", data="synthetic",
+                config=dict(workload=WORKLOADS[args.workload]["desc"], width=W, height=H, spp_per_step_per_gpu=per_step / world, max_bounces=sd.max_bounces, nee=True,
                             partition="disjoint global sample ranges per GPU, one NCCL reduce of the accumulation buffer per step" if world > 1 else "single GPU",
                             l2="per-step working set (path state: 16 slots/pixel x 196 B + queues = %.0f MB) exceeds L2 (126 MB); no flush needed" % (W * H * 16 * 248 / 1e6), build_seconds=round(build_s, 2),
                             device_ms_per_step=dev_ms / args.steps),

@@ -89,6 +89,7 @@ struct ptb_context
     int opt_dense = 1;            // slot-ordered wavefront kernels while most slots are live (0 = queue kernels throughout)
     int opt_dense_threshold = 60; // live slots per listed 32-slot group, in percent, below which ptb_render continues with the queue kernels
     int opt_shade_sort = -1;      // k_shade_ordered sorts each span's slots by shade kind: 1 yes, 0 no, <0 automatic (scenes with >= 2 surface material kinds)
+    int opt_tail_roles = 1;       // tail kernel with shadow / probe / next-bounce traversals on three warps side by side (0: one thread per slot)
     int opt_tail_threshold = -1;  // active slots at which ptb_render switches to the tail kernel (<0 automatic, 0 never)
     int profiling = 0;
     int second_moment = 0;

@@ -433,6 +433,7 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "nee_blocks") ctx->opt_nee_blocks = value;
     else if (n == "slots_per_pixel") ctx->opt_slots_per_pixel = value;
     else if (n == "tail_threshold") ctx->opt_tail_threshold = value;
+    else if (n == "tail_roles") ctx->opt_tail_roles = value;
     else if (n == "wide_collapse") ctx->scene.wide_collapse = value;  // takes effect at the next ptb_build
     else if (n == "dense") ctx->opt_dense = value;
     else if (n == "shade_sort") ctx->opt_shade_sort = value;

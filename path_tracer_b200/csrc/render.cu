@@ -79,7 +79,8 @@ struct RenderState
     float t_class_ms[8] = {0};
     uint32_t n_class[8] = {0};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
-    int tail_capacity = -1;  // resident threads of k_tail on this device
+    int tail_capacity = -1;  // slots the tail kernel (tail_kind: 1 = k_tail_roles, 0 = k_tail) keeps resident on this device
+    int tail_kind = -1;
 };
 
 // ---- device helpers ------------------------------------------------------------------------------------------------------
@@ -684,6 +685,112 @@ __global__ void __launch_bounds__(64) k_tail(RenderView V, Queues Q, uint32_t it
     }
 }
 
+// The tail with the three traversals of a bounce side by side.  What is left in the tail are a few thousand slots, some of them
+// on paths of up to 1024 bounces: the launch is as long as the longest chain of bounces, every bounce a chain of dependent loads
+// (L2 latency, not throughput).  Shadow ray, light probe and the NEXT bounce's closest-hit ray all depend only on the shade step
+// before them, so a block of three warps keeps 32 slots and runs them concurrently: warp 0 shades and extends, warp 1 traces the
+// shadow rays, warp 2 the probes (and their visibility rays).  Warp 0 adds the two contributions to the path's radiance in the
+// order of nee_slot_t, before the next shade or regeneration reads it: results are bit-identical to k_tail.
+template <bool BIN>
+__global__ void __launch_bounds__(96) k_tail_roles(RenderView V, Queues Q, uint32_t it)
+{
+    WfSet& S = Q.c->set[it % 3u];
+    const uint32_t b = it & 1u;
+    const uint32_t n_cont = S.n_cont, n_term = S.n_term;
+    const uint32_t lane = threadIdx.x & 31u, role = threadIdx.x >> 5;
+    const uint32_t idx = blockIdx.x * 32u + lane;
+    __shared__ uint32_t s_flags[32];
+    __shared__ float4 s_r[2][32];
+    unsigned long long n_ext = 0, n_sh = 0, n_pr = 0, n_ps = 0, n_paths = 0;
+    bool alive = idx < n_cont + n_term;
+    const uint32_t slot = !alive ? 0u : idx < n_cont ? Q.cont[b][idx] : Q.term[b][idx - n_cont];
+    bool need_regen = idx >= n_cont;
+    bool have_hit = false;  // warp 0: the slot's current ray was traced during the previous bounce's NEE
+    for (;;)
+    {
+        uint32_t flags = 0u;
+        if (role == 0u && alive)
+        {
+            if (!have_hit)
+            {
+                V3 o, d;
+                if (need_regen)
+                {
+                    if (regen_slot(V, slot, &o, &d) & WF_NEXT) ++n_paths;
+                    else alive = false;
+                }
+                else
+                {
+                    const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
+                    o = ex::v3(o4.x, o4.y, o4.z);
+                    d = ex::v3(d4.x, d4.y, d4.z);
+                }
+                if (alive)
+                {
+                    extend_ray_t<BIN>(V, slot, o, d);
+                    ++n_ext;
+                }
+            }
+            if (alive)
+            {
+                flags = shade_slot(V, slot);
+                n_pr += (flags & WF_PROBE_OUT) ? 1u : 0u;
+            }
+        }
+        if (role == 0u) s_flags[lane] = flags;
+        if (!__syncthreads_or(role == 0u && alive)) break;  // also publishes the records shade_slot wrote
+        flags = s_flags[lane];
+        if (role == 0u)
+        {
+            have_hit = false;
+            if (flags & WF_NEXT)
+            {
+                const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
+                extend_ray_t<BIN>(V, slot, ex::v3(o4.x, o4.y, o4.z), ex::v3(d4.x, d4.y, d4.z));
+                ++n_ext;
+                have_hit = true;
+            }
+        }
+        else if (flags & (role == 1u ? WF_SHADOW : WF_PROBE))
+        {
+            const float4 o4 = V.ray[slot].o;
+            const V3 o = ex::v3(o4.x, o4.y, o4.z);
+            float4 r = f4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (role == 1u)
+            {
+                shadow_contrib_t<BIN>(V, slot, o, &r);
+                ++n_sh;
+            }
+            else
+            {
+                n_ps += probe_contrib_t<BIN>(V, slot, o, &r);
+                ++n_pr;
+            }
+            s_r[role - 1u][lane] = r;
+        }
+        __syncthreads();
+        if (role == 0u)
+        {
+            if (flags & (WF_SHADOW | WF_PROBE))
+            {
+                float4 r = V.path[slot].radiance;
+                if (flags & WF_SHADOW) { const float4 c = s_r[0][lane]; r.x += c.x; r.y += c.y; r.z += c.z; }
+                if (flags & WF_PROBE) { const float4 c = s_r[1][lane]; r.x += c.x; r.y += c.y; r.z += c.z; }
+                V.path[slot].radiance = r;
+            }
+            need_regen = (flags & WF_TERM) != 0u;
+        }
+    }
+    if (n_ext | n_paths | n_sh | n_pr)
+    {
+        if (n_ext) atomicAdd(&Q.c->stat_extend, n_ext);
+        if (n_sh) atomicAdd(&Q.c->stat_shadow, n_sh);
+        if (n_pr) atomicAdd(&Q.c->stat_probe, n_pr);
+        if (n_ps) atomicAdd(&Q.c->stat_probe_shadow, n_ps);
+        if (n_paths) atomicAdd(&Q.c->stat_paths, n_paths);
+    }
+}
+
 // ---- probes (device code of raygen, run on small batches) -------------------------------------------------------------------
 __global__ void k_camera_rays(CameraDev cam, unsigned long long n, const float* st, float* o3, float* d3)
 {
@@ -980,11 +1087,13 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         PTB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         rs.poll_events.push_back(e);
     }
-    if (rs.tail_capacity < 0)
+    if (rs.tail_capacity < 0 || rs.tail_kind != (ctx->opt_tail_roles ? 1 : 0))
     {
+        rs.tail_kind = ctx->opt_tail_roles ? 1 : 0;
         int per_sm = 0;
-        PTB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tail<false>, 64, 0));
-        rs.tail_capacity = per_sm * 64 * ctx->sm_count;
+        if (ctx->opt_tail_roles) PTB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tail_roles<false>, 96, 0));
+        else PTB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tail<false>, 64, 0));
+        rs.tail_capacity = per_sm * (ctx->opt_tail_roles ? 32 : 64) * ctx->sm_count;
     }
     // switch to the tail kernel once every remaining slot fits on the device at once (0 disables, <0 = automatic)
     const uint32_t tail_threshold = ctx->opt_tail_threshold < 0 ? (uint32_t)rs.tail_capacity / 2u : (uint32_t)ctx->opt_tail_threshold;
@@ -1064,8 +1173,11 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             if (dense && (uint64_t)active * 100u < dense_pct * 32u * (uint64_t)f[3]) dense = false;
             if (to_tail)
             {
-                if (bin) k_tail<true><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);
-                else k_tail<false><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);  // active counts never grow: `active` bounds the queue at it+1
+                // active counts never grow: `active` bounds the queue at it+1
+                if (ctx->opt_tail_roles && bin) k_tail_roles<true><<<(active + 31u) / 32u, 96, 0, st>>>(V, Q, it + 1u);
+                else if (ctx->opt_tail_roles) k_tail_roles<false><<<(active + 31u) / 32u, 96, 0, st>>>(V, Q, it + 1u);
+                else if (bin) k_tail<true><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);
+                else k_tail<false><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);
                 PTB_CUDA(ctx, mark(5));
                 PTB_CUDA(ctx, cudaGetLastError());
                 rs.launches += 1;
