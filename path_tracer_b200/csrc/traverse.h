@@ -16,6 +16,11 @@
 #include "exact_math.h"
 #include "layout.h"
 
+// Development hook: a host-side tool (tools/stagecount.cpp) defines PTB_STAT to count the stages a ray runs through.
+#ifndef PTB_STAT
+#define PTB_STAT(stage)
+#endif
+
 namespace ptb {
 
 using ex::V3;
@@ -301,8 +306,10 @@ PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, uint2* stack)
                 // TLAS leaf (tlas.rs:88-100 / :132-139): exact leaf box with the current t_max, then Ray::transform
                 const float4 h0 = PTB_LDG4F(S.leaf_headers + (size_t)e.x * 2), h1 = PTB_LDG4F(S.leaf_headers + (size_t)e.x * 2 + 1);
                 float t_enter;
+                PTB_STAT(3);
                 if (ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), s.ray.o, s.ray.inv, s.t_max, &t_enter))
                 {
+                    PTB_STAT(4);
                     s.cur_inst = ex::bits(h1.w);
                     const uint32_t cw = ex::bits(h0.w);
                     float inv12[12] = {1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f};
@@ -351,6 +358,7 @@ PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, uint2* stack, bool al
         const uint4* np = S.wide + (size_t)s.node * 5;
         const uint4 q0 = PTB_LDG4U(np), q1 = PTB_LDG4U(np + 1), q2 = PTB_LDG4U(np + 2), q3 = PTB_LDG4U(np + 3), q4 = PTB_LDG4U(np + 4);
         s.node = TRAV_NONE;
+        PTB_STAT(s.cur_inst != TRAV_NONE ? 0 : 5);
         const uint32_t hits = wide_node_test(q0, q2, q3, q4, s.ray, s.t_max);
         const uint32_t imask = q0.w >> 24, lmask = q1.z & 0xffu;
         const uint32_t perm = xor_permute16((hits & imask) | ((hits & lmask) << 8), s.ray.oi);
@@ -391,6 +399,7 @@ PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, uint2* stack, bool al
         const uint32_t cw = ex::bits(h0.w);
         float t_enter = 0.0f;
         bool go = true;
+        PTB_STAT(1);
         // blas.rs:137-138 / :264 — exact reference leaf box, exact entry distance (the BLAS root is entered untested with
         // t_estimate = 0 by the closest-hit query, blas.rs:217)
         if (ANY || !(cw & LEAF_ROOT_FLAG)) go = ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), s.ray.o, s.ray.inv, s.t_max, &t_enter);
@@ -404,6 +413,7 @@ PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, uint2* stack, bool al
     // ---- T: one triangle ---------------------------------------------------------------------------------------------------
     if (s.tri_i < s.tri_end)
     {
+        PTB_STAT(2);
         const float4* pp = S.tri_planes + (size_t)s.tri_i * 3;
         const float4 a = PTB_LDG4F(pp), b = PTB_LDG4F(pp + 1), c = PTB_LDG4F(pp + 2);
         const float n0[4] = {a.x, a.y, a.z, a.w}, n1[4] = {b.x, b.y, b.z, b.w}, n2[4] = {c.x, c.y, c.z, c.w};

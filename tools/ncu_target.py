@@ -1,0 +1,20 @@
+"""Minimal render for ncu captures: one render of a scene, no warm-up, no trace probes.  python tools/ncu_target.py c3 16 [opt=value ...]"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import path_tracer_b200 as ptb
+from path_tracer_b200 import scenes
+
+name, spp = sys.argv[1], int(sys.argv[2])
+sd = {"c2": scenes.scene_c2, "c3": scenes.scene_c3, "c4": scenes.scene_c4}[name]()
+ctx = ptb.Context(0)
+ctx.upload(sd)
+for a in sys.argv[3:]:
+    k, v = a.split("=")
+    ctx.set_option(k, int(v))
+ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, sd.aspect)
+ctx.frame_begin(sd.width, sd.height)
+ctx.render(0, spp, seed=1, max_bounces=sd.max_bounces)
+ctx.synchronize()
+print("done", ctx.counters())
