@@ -153,6 +153,7 @@ struct Collapser
             const HostBlas& B = sc.blas[((const HostTlas*)tv.self)->blas_ids[n.a]];
             h.count = B.wide_root | (std::memcmp(n.inv, ident, sizeof(ident)) == 0 ? TLAS_IDENTITY_FLAG : 0u);
             h.first = inst_base + n.b;
+            std::memcpy(h.payload, n.inv, sizeof(h.payload));
         }
         else
         {
@@ -168,6 +169,7 @@ struct Collapser
                 sc.tri_planes.insert(sc.tri_planes.end(), t.n1, t.n1 + 4);
                 sc.tri_planes.insert(sc.tri_planes.end(), t.n2, t.n2 + 4);
                 sc.tri_prim.push_back(prim);
+                if (k == 0) { std::memcpy(h.payload, t.n0, 16); std::memcpy(h.payload + 4, t.n1, 16); std::memcpy(h.payload + 8, t.n2, 16); }
             }
         }
         sc.leaf_headers.push_back(h);

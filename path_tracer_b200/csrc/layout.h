@@ -50,21 +50,26 @@ struct WideNode
 };
 static_assert(sizeof(WideNode) == 80, "WideNode must be 80 bytes");
 
-// ---- leaf header, 32 B (2 x 128-bit loads) ----------------------------------------------------------------------
+// ---- leaf header, 32 B + 48 B payload (5 x 128-bit loads) ----------------------------------------------------------------------
 // BLAS level: exact AABB of one reference leaf (LeafSingle: the primitive's own box, blas_bvh.rs:69-74; Leaf: the union,
 // :78), count = number of primitives (bit 31 set: the leaf is the BLAS root -> closest-hit uses t_estimate = 0 and no
 // box test, blas.rs:217), first = first triangle slot (planes at tri_planes[3*slot..], prim id at tri_prim[slot]).
 // TLAS level: exact AABB of the reference TLAS leaf (AABB::transform of the BLAS root box, tlas_bvh.rs:94), count = wide root
 // of the BLAS (bit 31: inv_matrix is exactly the identity),
 // first = instance ordinal (row of the instance table).
+// The record carries what the traversal needs next in the same 80 bytes (5 x 128-bit loads issued together, no dependent
+// second fetch): BLAS level — the planes n0|d0, n1|d1, n2|d2 of the leaf's FIRST triangle (a copy of tri_planes[3*first..];
+// the other triangles of a multi-triangle leaf are read from tri_planes); TLAS level — the instance's inv_matrix.
 struct LeafHeader
 {
     float lo[3];
     uint32_t count;
     float hi[3];
     uint32_t first;
+    float payload[12];
 };
-static_assert(sizeof(LeafHeader) == 32, "LeafHeader must be 32 bytes");
+static_assert(sizeof(LeafHeader) == 80, "LeafHeader must be 80 bytes");
+constexpr uint32_t LEAF_F4 = 5;  // float4 per LeafHeader
 constexpr uint32_t LEAF_ROOT_FLAG = 0x80000000u;
 constexpr uint32_t TLAS_IDENTITY_FLAG = 0x80000000u;  // TLAS-level header: count = BLAS wide root | this flag
 
@@ -126,7 +131,7 @@ struct TlasDev
 struct SceneDev
 {
     const uint4* wide;           // WideNode[]
-    const float4* leaf_headers;  // LeafHeader[] as 2 x float4
+    const float4* leaf_headers;  // LeafHeader[] as LEAF_F4 x float4
     const float4* tri_planes;    // 3 float4 per triangle slot (n0,n1,n2), leaf order
     const uint32_t* tri_prim;    // triangle slot -> BLAS-local prim id
     const BinNode* bin;          // all BLAS binary nodes, then TLAS nodes

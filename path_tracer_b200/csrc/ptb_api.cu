@@ -144,7 +144,7 @@ static int upload_device(ptb_context* ctx)
 #define UP(dst, src, cnt) \
     if ((rc = to_device(ctx, dst, src, cnt)) != PTB_OK) return rc
     UP(ctx->d_wide, sc.wide, sc.wide.size() * 5);
-    UP(ctx->d_leaf_headers, sc.leaf_headers, sc.leaf_headers.size() * 2);
+    UP(ctx->d_leaf_headers, sc.leaf_headers, sc.leaf_headers.size() * ptb::LEAF_F4);
     UP(ctx->d_tri_planes, sc.tri_planes, sc.tri_planes.size() / 4);
     UP(ctx->d_tri_prim, sc.tri_prim, sc.tri_prim.size());
     UP(ctx->d_bin, sc.bin, sc.bin.size());

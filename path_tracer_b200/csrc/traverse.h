@@ -304,7 +304,8 @@ PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, uint2* stack)
             if (e.y & 0x80000000u)
             {
                 // TLAS leaf (tlas.rs:88-100 / :132-139): exact leaf box with the current t_max, then Ray::transform
-                const float4 h0 = PTB_LDG4F(S.leaf_headers + (size_t)e.x * 2), h1 = PTB_LDG4F(S.leaf_headers + (size_t)e.x * 2 + 1);
+                const float4* lp = S.leaf_headers + (size_t)e.x * LEAF_F4;
+                const float4 h0 = PTB_LDG4F(lp), h1 = PTB_LDG4F(lp + 1), i0 = PTB_LDG4F(lp + 2), i1 = PTB_LDG4F(lp + 3), i2 = PTB_LDG4F(lp + 4);
                 float t_enter;
                 PTB_STAT(3);
                 if (ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), s.ray.o, s.ray.inv, s.t_max, &t_enter))
@@ -312,15 +313,9 @@ PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, uint2* stack)
                     PTB_STAT(4);
                     s.cur_inst = ex::bits(h1.w);
                     const uint32_t cw = ex::bits(h0.w);
-                    float inv12[12] = {1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f};
-                    if (!(cw & TLAS_IDENTITY_FLAG))
-                    {
-                        const float4* ip = (const float4*)S.inst[s.cur_inst].inv;
-                        const float4 i0 = PTB_LDG4F(ip), i1 = PTB_LDG4F(ip + 1), i2 = PTB_LDG4F(ip + 2);
-                        inv12[0] = i0.x; inv12[1] = i0.y; inv12[2] = i0.z; inv12[3] = i0.w; inv12[4] = i1.x; inv12[5] = i1.y;
-                        inv12[6] = i1.z; inv12[7] = i1.w; inv12[8] = i2.x; inv12[9] = i2.y; inv12[10] = i2.z; inv12[11] = i2.w;
-                    }
-                    // the arithmetic of Ray::transform is carried out even for the identity (x*1 + y*0 + ... decides the sign of zeros)
+                    // inv_matrix travels in the leaf record (no dependent InstanceRow fetch); the arithmetic of Ray::transform is
+                    // carried out even for the identity (x*1 + y*0 + ... decides the sign of zeros)
+                    const float inv12[12] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w, i2.x, i2.y, i2.z, i2.w};
                     transform_ray_reuse(s.ray, s.ow, s.dw, s.invw, inv12);
                     s.blas_sp = s.sp;
                     s.node = cw & ~TLAS_IDENTITY_FLAG;
@@ -389,13 +384,17 @@ PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, uint2* stack, bool al
         }
     }
     // ---- L: one reference leaf of the current BLAS node -------------------------------------------------------------------
+    float4 pa = {0.0f, 0.0f, 0.0f, 0.0f}, pb = pa, pc = pa;  // planes of the leaf's first triangle, fetched with its header
+    bool fresh = false;
     if (s.tri_i >= s.tri_end && s.lh)
     {
         const int p = hi_bit(s.lh);
         s.lh &= ~(1u << p);
         const uint32_t sl = (uint32_t)p ^ s.ray.oi;
         const uint32_t hidx = s.leaf_base + popc32(s.lmask & ((1u << sl) - 1u));
-        const float4 h0 = PTB_LDG4F(S.leaf_headers + (size_t)hidx * 2), h1 = PTB_LDG4F(S.leaf_headers + (size_t)hidx * 2 + 1);
+        const float4* lp = S.leaf_headers + (size_t)hidx * LEAF_F4;
+        const float4 h0 = PTB_LDG4F(lp), h1 = PTB_LDG4F(lp + 1);
+        pa = PTB_LDG4F(lp + 2); pb = PTB_LDG4F(lp + 3); pc = PTB_LDG4F(lp + 4);
         const uint32_t cw = ex::bits(h0.w);
         float t_enter = 0.0f;
         bool go = true;
@@ -408,14 +407,19 @@ PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, uint2* stack, bool al
             s.tri_i = ex::bits(h1.w);
             s.tri_end = s.tri_i + (cw & ~LEAF_ROOT_FLAG);
             s.t_enter = t_enter;
+            fresh = true;
         }
     }
     // ---- T: one triangle ---------------------------------------------------------------------------------------------------
     if (s.tri_i < s.tri_end)
     {
         PTB_STAT(2);
-        const float4* pp = S.tri_planes + (size_t)s.tri_i * 3;
-        const float4 a = PTB_LDG4F(pp), b = PTB_LDG4F(pp + 1), c = PTB_LDG4F(pp + 2);
+        float4 a = pa, b = pb, c = pc;
+        if (!fresh)
+        {
+            const float4* pp = S.tri_planes + (size_t)s.tri_i * 3;
+            a = PTB_LDG4F(pp); b = PTB_LDG4F(pp + 1); c = PTB_LDG4F(pp + 2);
+        }
         const float n0[4] = {a.x, a.y, a.z, a.w}, n1[4] = {b.x, b.y, b.z, b.w}, n2[4] = {c.x, c.y, c.z, c.w};
         if (ANY)
         {

@@ -96,7 +96,7 @@ void emu_stats(void* h, uint64_t* out8)
     out8[0] = sc.wide.size();
     out8[1] = sc.leaf_headers.size();
     out8[2] = sc.tri_prim.size();
-    out8[3] = sc.wide.size() * 80 + sc.leaf_headers.size() * 32 + sc.tri_prim.size() * 52;
+    out8[3] = sc.wide.size() * 80 + sc.leaf_headers.size() * sizeof(LeafHeader) + sc.tri_prim.size() * 52;
     out8[4] = 0;
     for (auto& B : sc.blas) out8[4] = std::max<uint64_t>(out8[4], B.wide_depth);
     out8[4] += sc.tlas[0].wide_depth;

@@ -4,6 +4,9 @@ import sys
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import path_tracer_b200 as ptb
+from path_tracer_b200 import api as _api
+if os.environ.get("PTB_LIB"):  # A/B runs of two builds in one gpurun call (tuning aid)
+    _api.lib_path = lambda: os.environ["PTB_LIB"]
 from path_tracer_b200 import scenes
 
 name, spp = sys.argv[1], int(sys.argv[2])
