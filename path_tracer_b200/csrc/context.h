@@ -86,10 +86,12 @@ struct ptb_context
     int opt_node_quorum = 8;      // lanes of a warp that must want the node stage before it runs (1 = never postponed)
     int opt_extend_blocks = 6, opt_nee_blocks = 5;  // resident blocks per SM (launch bounds -> register cap) of k_extend / k_nee
     int opt_slots_per_pixel = 16;  // path slots per pixel (1..16): more slots = more paths in flight, fewer and larger wavefront iterations
+    int opt_wavefront_groups = 1; // independent wavefronts per render, each over 1/G of the slots on its own stream (1..8)
     int opt_dense = 1;            // slot-ordered wavefront kernels while most slots are live (0 = queue kernels throughout)
     int opt_dense_threshold = 60; // live slots per listed 32-slot group, in percent, below which ptb_render continues with the queue kernels
     int opt_shade_sort = -1;      // k_shade_ordered sorts each span's slots by shade kind: 1 yes, 0 no, <0 automatic (scenes with >= 2 surface material kinds)
     int opt_tail_roles = 1;       // tail kernel with shadow / probe / next-bounce traversals on three warps side by side (0: one thread per slot)
+    int opt_tail_slots_per_block = 32;  // k_tail_roles: slots per block of three warps (1..32)
     int opt_tail_threshold = -1;  // active slots at which ptb_render switches to the tail kernel (<0 automatic, 0 never)
     int profiling = 0;
     int second_moment = 0;

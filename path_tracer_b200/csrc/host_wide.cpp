@@ -147,11 +147,12 @@ struct Collapser
         if (is_tlas)
         {
             const HostTlasNode& n = ((const HostTlas*)tv.self)->nodes[bin_id];
-            // count = wide root of the instance's BLAS | TLAS_IDENTITY_FLAG when inv_matrix is bit-for-bit the identity with a +0
-            // translation: the traversal then needs no InstanceRow access to enter the instance
-            static const float ident[12] = {1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f};
+            // count = wide root of the instance's BLAS, or the direct-leaf encoding when that root holds only one or two leaves
             const HostBlas& B = sc.blas[((const HostTlas*)tv.self)->blas_ids[n.a]];
-            h.count = B.wide_root | (std::memcmp(n.inv, ident, sizeof(ident)) == 0 ? TLAS_IDENTITY_FLAG : 0u);
+            const WideNode& rn = sc.wide[B.wide_root];
+            if (rn.imask == 0 && (uint32_t)__builtin_popcount(rn.lmask) <= TLAS_DIRECT_MAX_LEAVES && rn.leaf_base < (1u << TLAS_DIRECT_BASE_BITS))
+                h.count = TLAS_DIRECT_FLAG | ((uint32_t)rn.lmask << TLAS_DIRECT_BASE_BITS) | rn.leaf_base;
+            else h.count = B.wide_root;
             h.first = inst_base + n.b;
             std::memcpy(h.payload, n.inv, sizeof(h.payload));
         }

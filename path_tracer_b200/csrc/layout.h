@@ -55,7 +55,7 @@ static_assert(sizeof(WideNode) == 80, "WideNode must be 80 bytes");
 // :78), count = number of primitives (bit 31 set: the leaf is the BLAS root -> closest-hit uses t_estimate = 0 and no
 // box test, blas.rs:217), first = first triangle slot (planes at tri_planes[3*slot..], prim id at tri_prim[slot]).
 // TLAS level: exact AABB of the reference TLAS leaf (AABB::transform of the BLAS root box, tlas_bvh.rs:94), count = wide root
-// of the BLAS (bit 31: inv_matrix is exactly the identity),
+// of the BLAS (or the direct-leaf encoding, TLAS_DIRECT_FLAG below),
 // first = instance ordinal (row of the instance table).
 // The record carries what the traversal needs next in the same 80 bytes (5 x 128-bit loads issued together, no dependent
 // second fetch): BLAS level — the planes n0|d0, n1|d1, n2|d2 of the leaf's FIRST triangle (a copy of tri_planes[3*first..];
@@ -71,7 +71,12 @@ struct LeafHeader
 static_assert(sizeof(LeafHeader) == 80, "LeafHeader must be 80 bytes");
 constexpr uint32_t LEAF_F4 = 5;  // float4 per LeafHeader
 constexpr uint32_t LEAF_ROOT_FLAG = 0x80000000u;
-constexpr uint32_t TLAS_IDENTITY_FLAG = 0x80000000u;  // TLAS-level header: count = BLAS wide root | this flag
+// TLAS-level header: count = wide root of the BLAS — or, for a BLAS whose root node holds nothing but at most
+// TLAS_DIRECT_MAX_LEAVES leaves (a quad, a single triangle), this flag | lmask << 23 | leaf_base: the traversal then goes
+// straight to the exact leaf tests and never fetches or tests that node (its boxes could only repeat what the instance box said)
+constexpr uint32_t TLAS_DIRECT_FLAG = 0x80000000u;
+constexpr uint32_t TLAS_DIRECT_MAX_LEAVES = 2;
+constexpr uint32_t TLAS_DIRECT_BASE_BITS = 23;
 
 // ---- instance table row, 128 B ------------------------------------------------------------------------------------
 struct InstanceRow

@@ -28,7 +28,11 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, ui
     // Near the end of the queue the batch shrinks to what the idle lanes need right now, so that no warp is left holding a
     // long private backlog while the others have run dry.
     constexpr uint32_t BATCH = 64;
-    const uint32_t fine_below = (gridDim.x * blockDim.x >> 5) * (2u * BATCH);
+    const uint32_t n_warps = gridDim.x * blockDim.x >> 5;
+    const uint32_t fine_below = n_warps * (2u * BATCH);
+    // a queue shorter than one full set of lanes is spread evenly over the warps of the grid: a warp runs as long as the slowest
+    // of its rays, and a launch as long as its slowest warp
+    const uint32_t fair = max(1u, (total + n_warps - 1u) / n_warps);
     uint32_t wbase = 0, wend = 0, seen = 0;
     bool global_more = total > 0u;
     for (;;)
@@ -45,7 +49,7 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, ui
             if (!idle) break;
             if (wbase >= wend)
             {
-                const uint32_t want = (total - seen > fine_below) ? BATCH : (uint32_t)__popc(idle);
+                const uint32_t want = (total - seen > fine_below) ? BATCH : min((uint32_t)__popc(idle), fair);
                 uint32_t base = 0;
                 if (lane == 0u) base = atomicAdd(cursor, want);
                 base = __shfl_sync(FULL, base, 0);

@@ -434,8 +434,10 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "slots_per_pixel") ctx->opt_slots_per_pixel = value;
     else if (n == "tail_threshold") ctx->opt_tail_threshold = value;
     else if (n == "tail_roles") ctx->opt_tail_roles = value;
+    else if (n == "tail_slots_per_block") ctx->opt_tail_slots_per_block = value;
     else if (n == "wide_collapse") ctx->scene.wide_collapse = value;  // takes effect at the next ptb_build
     else if (n == "dense") ctx->opt_dense = value;
+    else if (n == "wavefront_groups") ctx->opt_wavefront_groups = value;
     else if (n == "shade_sort") ctx->opt_shade_sort = value;
     else if (n == "dense_threshold") ctx->opt_dense_threshold = value;
     else if (n == "nee_refill_below") ctx->opt_nee_refill_below = value < 1 ? 1 : (value > 32 ? 32 : value);

@@ -47,11 +47,14 @@ struct Queues
     uint32_t* nee;      // slot | NEE_SHADOW_BIT | NEE_PROBE_BIT
     uint32_t* grp[2];   // slot-ordered mode: ascending list of the 32-slot groups that still hold a live slot, double-buffered like cont/term
     uint32_t* state;    // slot-ordered mode: per-slot WF_* flags of the last shade (WF_NEXT / WF_TERM / 0 = no samples left, | WF_SHADOW | WF_PROBE)
-    uint32_t npix;
+    uint32_t npix;       // queue capacity and stride of the material queues: the number of slots of this wavefront group
+    uint32_t slot_base;  // the group's slots are [slot_base, slot_end); slot_base is a multiple of 32
+    uint32_t slot_end;
     WfCounters* c;
 };
 
 constexpr uint32_t POLL_RING = 8192;
+constexpr int MAX_GROUPS = 8;  // independent wavefronts per render (wavefront_groups), each on its own stream
 
 struct RenderState
 {
@@ -69,7 +72,9 @@ struct RenderState
     DBuf<unsigned long long> volset;
     DBuf<WfCounters> counters;
     float4* accum = nullptr;  // bound or own
-    uint32_t* h_flags = nullptr;  // pinned, POLL_RING x 4 (n_cont, n_term, n_nee, n_grp of every iteration)
+    uint32_t* h_flags = nullptr;  // pinned, MAX_GROUPS x POLL_RING x 4 (n_cont, n_term, n_nee, n_grp of every iteration of every group)
+    std::vector<cudaStream_t> group_streams;  // streams of the wavefront groups 1.. (group 0 runs on the context stream)
+    std::vector<cudaEvent_t> group_events;    // fork / join events
     uint32_t log_iters = 0;       // iterations recorded in h_flags by the last ptb_render
     std::vector<cudaEvent_t> poll_events;
     std::vector<cudaEvent_t> prof_events;
@@ -118,17 +123,18 @@ __device__ __forceinline__ bool fetch_chunk(uint32_t* cursor, uint32_t nchunks, 
 
 __global__ void __launch_bounds__(128) k_init(RenderView V, Queues Q, const uint32_t* id_px)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= Q.npix) return;  // Q.npix = number of slots
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= Q.npix) return;  // Q.npix = number of slots of this group
+    const uint32_t i = Q.slot_base + j;
     V.ray[i].o.w = 0.0f;  // no sample in flight
     V.ray[i].d.w = 0.0f;  // samples started = 0
     V.accum[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     if (V.accum_sq) V.accum_sq[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     V.id[i] = V.K == 1u ? id_px[i] : 0u;  // one slot per pixel: the slot continues the pixel's id history (main.rs:206)
-    Q.term[0][i] = i;
+    Q.term[0][j] = i;
     Q.state[i] = WF_TERM;
-    if ((i & 31u) == 0u) Q.grp[0][i >> 5] = i >> 5;
-    if (i == 0)
+    if ((j & 31u) == 0u) Q.grp[0][j >> 5] = i >> 5;
+    if (j == 0)
     {
         for (int s = 0; s < 3; ++s) Q.c->set[s] = WfSet{};
         Q.c->set[0].n_term = Q.npix;
@@ -494,7 +500,7 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
                 const uint32_t gi = first + row * 8u + warp;
                 const uint32_t slot = gi < n_grp ? grp[gi] * 32u + lane : 0xffffffffu;
                 uint32_t kind = 7u;  // not live
-                if (slot < Q.npix && (Q.state[slot] & WF_NEXT)) kind = min(V.hit[slot].kind, 6u);
+                if (slot < Q.slot_end && (Q.state[slot] & WF_NEXT)) kind = min(V.hit[slot].kind, 6u);
                 my_kind[row] = kind;
     #pragma unroll
                 for (uint32_t k = 0; k < 7u; ++k)
@@ -563,7 +569,7 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
             {
                 const uint32_t gi = first + row * 8u + warp;
                 const uint32_t slot = gi < n_grp ? grp[gi] * 32u + lane : 0xffffffffu;
-                if (slot < Q.npix && (Q.state[slot] & WF_NEXT))
+                if (slot < Q.slot_end && (Q.state[slot] & WF_NEXT))
                 {
                     const uint32_t flags = shade_slot(V, slot);
                     Q.state[slot] = flags;
@@ -582,7 +588,7 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
             const uint32_t gi = first + row * 8u + warp;
             const uint32_t slot = gi < n_grp ? grp[gi] * 32u + lane : 0xffffffffu;
             // every non-zero flag word of a listed group now is this pass's: the pass ran on the WF_NEXT slots and the others were 0
-            const uint32_t flags = slot < Q.npix ? Q.state[slot] : 0u;
+            const uint32_t flags = slot < Q.slot_end ? Q.state[slot] : 0u;
             const unsigned mt = __ballot_sync(0xffffffffu, (flags & WF_TERM) != 0u), mc = __ballot_sync(0xffffffffu, (flags & WF_NEXT) != 0u);
             const unsigned mn = __ballot_sync(0xffffffffu, (flags & (WF_SHADOW | WF_PROBE)) != 0u);
             if (lane == 0u)
@@ -615,7 +621,7 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
             const uint32_t gi = first + row * 8u + warp, e = row * 8u + warp;
             const uint32_t g = gi < n_grp ? grp[gi] : 0xffffffffu;
             const uint32_t slot = gi < n_grp ? g * 32u + lane : 0xffffffffu;
-            const uint32_t flags = slot < Q.npix ? Q.state[slot] : 0u;  // written by this thread in the first pass
+            const uint32_t flags = slot < Q.slot_end ? Q.state[slot] : 0u;  // written by this thread in the first pass
             const unsigned lt = (1u << lane) - 1u;
             const unsigned mt = __ballot_sync(0xffffffffu, (flags & WF_TERM) != 0u), mc = __ballot_sync(0xffffffffu, (flags & WF_NEXT) != 0u);
             const unsigned mn = __ballot_sync(0xffffffffu, (flags & (WF_SHADOW | WF_PROBE)) != 0u);
@@ -692,17 +698,19 @@ __global__ void __launch_bounds__(64) k_tail(RenderView V, Queues Q, uint32_t it
 // shadow rays, warp 2 the probes (and their visibility rays).  Warp 0 adds the two contributions to the path's radiance in the
 // order of nee_slot_t, before the next shade or regeneration reads it: results are bit-identical to k_tail.
 template <bool BIN>
-__global__ void __launch_bounds__(96) k_tail_roles(RenderView V, Queues Q, uint32_t it)
+__global__ void __launch_bounds__(96) k_tail_roles(RenderView V, Queues Q, uint32_t it, uint32_t spb)
 {
     WfSet& S = Q.c->set[it % 3u];
     const uint32_t b = it & 1u;
     const uint32_t n_cont = S.n_cont, n_term = S.n_term;
     const uint32_t lane = threadIdx.x & 31u, role = threadIdx.x >> 5;
-    const uint32_t idx = blockIdx.x * 32u + lane;
+    // spb slots per block (lanes >= spb idle): a bounce of the block lasts as long as the slowest of its slots, so fewer slots
+    // per block shorten the chain when the device has warps to spare
+    const uint32_t idx = blockIdx.x * spb + lane;
     __shared__ uint32_t s_flags[32];
     __shared__ float4 s_r[2][32];
     unsigned long long n_ext = 0, n_sh = 0, n_pr = 0, n_ps = 0, n_paths = 0;
-    bool alive = idx < n_cont + n_term;
+    bool alive = lane < spb && idx < n_cont + n_term;
     const uint32_t slot = !alive ? 0u : idx < n_cont ? Q.cont[b][idx] : Q.term[b][idx - n_cont];
     bool need_regen = idx >= n_cont;
     bool have_hit = false;  // warp 0: the slot's current ray was traced during the previous bounce's NEE
@@ -837,6 +845,8 @@ void render_state_destroy(ptb_context* ctx)
     if (!rs) return;
     for (auto e : rs->poll_events) cudaEventDestroy(e);
     for (auto e : rs->prof_events) cudaEventDestroy(e);
+    for (auto e : rs->group_events) cudaEventDestroy(e);
+    for (auto s : rs->group_streams) cudaStreamDestroy(s);
     if (rs->ev_begin) cudaEventDestroy(rs->ev_begin);
     if (rs->ev_end) cudaEventDestroy(rs->ev_end);
     if (rs->h_flags) cudaFreeHost(rs->h_flags);
@@ -956,15 +966,15 @@ int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height)
     PTB_CUDA(ctx, rs.position.resize(npix));
     PTB_CUDA(ctx, rs.id.resize(npix));
     if (ctx->second_moment) PTB_CUDA(ctx, rs.accum_sq.resize(npix));
-    PTB_CUDA(ctx, rs.counters.resize(1));
-    if (!rs.h_flags) PTB_CUDA(ctx, cudaHostAlloc((void**)&rs.h_flags, POLL_RING * 4 * sizeof(uint32_t), cudaHostAllocDefault));
+    PTB_CUDA(ctx, rs.counters.resize(MAX_GROUPS));
+    if (!rs.h_flags) PTB_CUDA(ctx, cudaHostAlloc((void**)&rs.h_flags, (size_t)MAX_GROUPS * POLL_RING * 4 * sizeof(uint32_t), cudaHostAllocDefault));
     if (!rs.ev_begin) { PTB_CUDA(ctx, cudaEventCreate(&rs.ev_begin)); PTB_CUDA(ctx, cudaEventCreate(&rs.ev_end)); }
     if (!bound) rs.accum = rs.accum_own.p;
     PTB_CUDA(ctx, cudaMemsetAsync(rs.accum, 0, (size_t)npix * 16, ctx->stream));
     if (ctx->second_moment) PTB_CUDA(ctx, cudaMemsetAsync(rs.accum_sq.p, 0, (size_t)npix * 16, ctx->stream));
     PTB_CUDA(ctx, cudaMemsetAsync(rs.position.p, 0, (size_t)npix * 16, ctx->stream));
     PTB_CUDA(ctx, cudaMemsetAsync(rs.id.p, 0, (size_t)npix * 4, ctx->stream));
-    if (fresh) PTB_CUDA(ctx, cudaMemsetAsync(rs.counters.p, 0, sizeof(WfCounters), ctx->stream));  // statistics persist until ptb_reset_counters
+    if (fresh) PTB_CUDA(ctx, cudaMemsetAsync(rs.counters.p, 0, sizeof(WfCounters) * MAX_GROUPS, ctx->stream));  // statistics persist until ptb_reset_counters
     return PTB_OK;
 }
 
@@ -1056,16 +1066,53 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     V.position = rs.s_position.p; V.id = rs.s_id.p;
     V.ray = rs.ray.p; V.path = rs.path.p; V.hit = rs.hit.p; V.shadow = rs.shadow.p; V.probe = rs.probe.p;
     V.volset = ctx->scene.volumes.empty() ? nullptr : rs.volset.p;
-    Queues Q{};
-    Q.cont[0] = rs.q_cont0.p; Q.cont[1] = rs.q_cont1.p; Q.term[0] = rs.q_term0.p; Q.term[1] = rs.q_term1.p;
-    Q.mat = rs.q_mat.p; Q.nee = rs.q_nee.p; Q.state = rs.slot_state.p; Q.grp[0] = rs.q_grp0.p; Q.grp[1] = rs.q_grp1.p;
-    Q.npix = rs.n_slots;  // queue capacity and stride: one entry per slot
-    Q.c = rs.counters.p;
-
     const int threads = 128;
     const int grid = ctx->sm_count * std::max(1, ctx->opt_blocks_per_sm);
     cudaStream_t st = ctx->stream;
     const bool prof = ctx->profiling != 0;
+    const bool sort = ctx->opt_sort_materials != 0, bin = V.extend_kernel != 0u;
+
+    // Wavefront groups: the slots are split into G contiguous ranges (boundaries at multiples of 32), each an independent
+    // wavefront with its own queues and counters on its own stream.  Slots never interact, so results do not depend on G.  While
+    // most slots are live the groups simply share the device; once few paths remain — every launch then lasts as long as the
+    // slowest ray in it, a chain of dependent loads, whatever the number of rays — the G chains overlap instead of following one
+    // another.  Per-launch profiling (CUDA events between consecutive launches of one stream) needs a single group.
+    const int G = prof ? 1 : std::max(1, std::min<int>(std::min(MAX_GROUPS, ctx->opt_wavefront_groups), (int)(n_slots / 4096u) + 1));
+    while ((int)rs.group_streams.size() < G - 1)
+    {
+        cudaStream_t s2;
+        PTB_CUDA(ctx, cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking));
+        rs.group_streams.push_back(s2);
+    }
+    while ((int)rs.group_events.size() < MAX_GROUPS + 1)
+    {
+        cudaEvent_t e;
+        PTB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        rs.group_events.push_back(e);
+    }
+    struct GroupRun
+    {
+        Queues Q;
+        cudaStream_t st;
+        uint32_t it = 0;
+        bool dense = false, done = false;
+        uint32_t* h_flags = nullptr;
+        uint32_t tail_threshold = 0;
+    };
+    GroupRun gr[MAX_GROUPS];
+    for (int g = 0; g < G; ++g)
+    {
+        const uint32_t b0 = (uint32_t)((n_slots * (size_t)g / (size_t)G) & ~(size_t)31), b1 = g + 1 == G ? (uint32_t)n_slots : (uint32_t)((n_slots * (size_t)(g + 1) / (size_t)G) & ~(size_t)31);
+        Queues& Q = gr[g].Q;
+        Q.cont[0] = rs.q_cont0.p + b0; Q.cont[1] = rs.q_cont1.p + b0; Q.term[0] = rs.q_term0.p + b0; Q.term[1] = rs.q_term1.p + b0;
+        Q.mat = rs.q_mat.p + (size_t)b0 * 7; Q.nee = rs.q_nee.p + b0; Q.state = rs.slot_state.p; Q.grp[0] = rs.q_grp0.p + (b0 >> 5); Q.grp[1] = rs.q_grp1.p + (b0 >> 5);
+        Q.npix = b1 - b0;  // queue capacity and stride: one entry per slot of the group
+        Q.slot_base = b0; Q.slot_end = b1;
+        Q.c = rs.counters.p + g;
+        gr[g].st = g == 0 ? st : rs.group_streams[g - 1];
+        gr[g].h_flags = rs.h_flags + (size_t)g * POLL_RING * 4;
+    }
+
     size_t prof_used = 0;
     std::vector<int> prof_class;
     auto mark = [&](int cls) -> cudaError_t {
@@ -1081,7 +1128,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         return cudaEventRecord(rs.prof_events[prof_used++], st);
     };
     const uint32_t NEV = 64;
-    while (rs.poll_events.size() < NEV)
+    while (rs.poll_events.size() < NEV * MAX_GROUPS)
     {
         cudaEvent_t e;
         PTB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -1095,19 +1142,22 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         else PTB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tail<false>, 64, 0));
         rs.tail_capacity = per_sm * (ctx->opt_tail_roles ? 32 : 64) * ctx->sm_count;
     }
-    // switch to the tail kernel once every remaining slot fits on the device at once (0 disables, <0 = automatic)
-    const uint32_t tail_threshold = ctx->opt_tail_threshold < 0 ? (uint32_t)rs.tail_capacity / 2u : (uint32_t)ctx->opt_tail_threshold;
+    // switch to the tail kernel once every remaining slot (of all groups together) fits on the device at once (0 disables, <0 = automatic)
+    const uint32_t tail_threshold = (ctx->opt_tail_threshold < 0 ? (uint32_t)rs.tail_capacity / 2u : (uint32_t)ctx->opt_tail_threshold) / (uint32_t)G;
 
     PTB_CUDA(ctx, cudaEventRecord(rs.ev_begin, st));
     PTB_CUDA(ctx, mark(-1));
-    k_init<<<(rs.n_slots + threads - 1) / threads, threads, 0, st>>>(V, Q, rs.id.p);
+    for (int g = 0; g < G; ++g) k_init<<<(gr[g].Q.npix + threads - 1) / threads, threads, 0, st>>>(V, gr[g].Q, rs.id.p);
     PTB_CUDA(ctx, mark(1));
-    rs.launches += 1;
-    const bool sort = ctx->opt_sort_materials != 0, bin = V.extend_kernel != 0u;
+    rs.launches += G;
+    if (G > 1)
+    {
+        PTB_CUDA(ctx, cudaEventRecord(rs.group_events[MAX_GROUPS], st));  // fork
+        for (int g = 1; g < G; ++g) PTB_CUDA(ctx, cudaStreamWaitEvent(gr[g].st, rs.group_events[MAX_GROUPS], 0));
+    }
     const uint32_t LAG = 8;
     rs.log_iters = 0;
     // k_shade_ordered while the listed groups are at least dense_threshold % full of live slots (never for the reference-order variant)
-    bool dense = !bin && ctx->opt_dense != 0;
     const uint64_t dense_pct = (uint64_t)std::max(0, std::min(100, ctx->opt_dense_threshold));
     const int shade_grid = ctx->sm_count * 8;
     // span-local sort by shade kind: worth its extra passes when warps would otherwise mix surface materials (auto: >= 2 non-emissive kinds)
@@ -1118,40 +1168,47 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         for (const auto& b : ctx->scene.blas_desc) kinds |= 1u << std::min<uint32_t>(b.material.kind, 7u);
         shade_sort = __builtin_popcount(kinds & ~2u) >= 2;  // kind 1 = Emissive
     }
-    for (uint32_t it = 0;; ++it)
-    {
+    for (int g = 0; g < G; ++g) gr[g].dense = !bin && ctx->opt_dense != 0;
+
+    // one wavefront iteration of group g (three launches on its stream) and its poll; sets done when the group has finished
+    auto step_group = [&](int g) -> int {
+        GroupRun& R = gr[g];
+        const Queues& Q = R.Q;
+        cudaStream_t gs = R.st;
+        const uint32_t it = R.it;
+        const bool dense = R.dense;
         const int rb = ctx->opt_refill_below, rbn = ctx->opt_nee_refill_below, nq = ctx->opt_node_quorum;
-        if (bin) k_extend_bin<<<grid, threads, 0, st>>>(V, Q, it);
+        if (bin) k_extend_bin<<<grid, threads, 0, gs>>>(V, Q, it);
         else
         {
-            const int g = ctx->sm_count * ctx->opt_extend_blocks, so = dense ? -1 : (sort ? 1 : 0);
+            const int eg = ctx->sm_count * ctx->opt_extend_blocks, so = dense ? -1 : (sort ? 1 : 0);
             switch (ctx->opt_extend_blocks)
             {
-            case 5: k_extend<5><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
-            case 7: k_extend<7><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
-            case 8: k_extend<8><<<g, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
-            default: k_extend<6><<<ctx->sm_count * 6, threads, 0, st>>>(V, Q, it, so, rb, nq); break;
+            case 5: k_extend<5><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
+            case 7: k_extend<7><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
+            case 8: k_extend<8><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
+            default: k_extend<6><<<ctx->sm_count * 6, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
             }
         }
         PTB_CUDA(ctx, mark(2));
-        if (dense && shade_sort) k_shade_ordered<true><<<shade_grid, 256, 0, st>>>(V, Q, it);
-        else if (dense) k_shade_ordered<false><<<shade_grid, 256, 0, st>>>(V, Q, it);
-        else k_shade<<<grid, threads, 0, st>>>(V, Q, it);
+        if (dense && shade_sort) k_shade_ordered<true><<<shade_grid, 256, 0, gs>>>(V, Q, it);
+        else if (dense) k_shade_ordered<false><<<shade_grid, 256, 0, gs>>>(V, Q, it);
+        else k_shade<<<grid, threads, 0, gs>>>(V, Q, it);
         PTB_CUDA(ctx, mark(3));
         rs.launches += 2;
         if (V.enable_nee)
         {
-            if (bin) k_nee_bin<<<grid, threads, 0, st>>>(V, Q, it);
+            if (bin) k_nee_bin<<<grid, threads, 0, gs>>>(V, Q, it);
             else
             {
-                const int g = ctx->sm_count * ctx->opt_nee_blocks;
+                const int ng = ctx->sm_count * ctx->opt_nee_blocks;
                 switch (ctx->opt_nee_blocks)
                 {
-                case 4: k_nee<4><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
-                case 7: k_nee<7><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
-                case 8: k_nee<8><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
-                case 6: k_nee<6><<<g, threads, 0, st>>>(V, Q, it, rbn, nq); break;
-                default: k_nee<5><<<ctx->sm_count * 5, threads, 0, st>>>(V, Q, it, rbn, nq); break;
+                case 4: k_nee<4><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
+                case 7: k_nee<7><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
+                case 8: k_nee<8><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
+                case 6: k_nee<6><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
+                default: k_nee<5><<<ctx->sm_count * 5, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
                 }
             }
             PTB_CUDA(ctx, mark(4));
@@ -1159,31 +1216,50 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         }
         PTB_CUDA(ctx, cudaGetLastError());
         // active-slot count of the next iteration, read LAG iterations behind the launch front
-        PTB_CUDA(ctx, cudaMemcpyAsync(&rs.h_flags[(it % POLL_RING) * 4], &rs.counters.p->set[(it + 1u) % 3u].n_cont, 16, cudaMemcpyDeviceToHost, st));
-        PTB_CUDA(ctx, cudaEventRecord(rs.poll_events[it % NEV], st));
-        rs.log_iters = it + 1;
+        PTB_CUDA(ctx, cudaMemcpyAsync(&R.h_flags[(it % POLL_RING) * 4], &Q.c->set[(it + 1u) % 3u].n_cont, 16, cudaMemcpyDeviceToHost, gs));
+        PTB_CUDA(ctx, cudaEventRecord(rs.poll_events[(size_t)g * NEV + it % NEV], gs));
+        if (g == 0) rs.log_iters = it + 1;
+        R.it = it + 1;
         if (it >= LAG)
         {
-            PTB_CUDA(ctx, cudaEventSynchronize(rs.poll_events[(it - LAG) % NEV]));
-            const uint32_t* f = &rs.h_flags[((it - LAG) % POLL_RING) * 4];
+            PTB_CUDA(ctx, cudaEventSynchronize(rs.poll_events[(size_t)g * NEV + (it - LAG) % NEV]));
+            const uint32_t* f = &R.h_flags[((it - LAG) % POLL_RING) * 4];
             const uint32_t active = f[0] + f[1];
-            if (active == 0u) break;
+            if (active == 0u) { R.done = true; return PTB_OK; }
             const bool to_tail = active <= tail_threshold;
             // live slots scattered thinly over the listed groups: the queue shade kernel from the next iteration on (the queues are valid as they are)
-            if (dense && (uint64_t)active * 100u < dense_pct * 32u * (uint64_t)f[3]) dense = false;
+            if (dense && (uint64_t)active * 100u < dense_pct * 32u * (uint64_t)f[3]) R.dense = false;
             if (to_tail)
             {
                 // active counts never grow: `active` bounds the queue at it+1
-                if (ctx->opt_tail_roles && bin) k_tail_roles<true><<<(active + 31u) / 32u, 96, 0, st>>>(V, Q, it + 1u);
-                else if (ctx->opt_tail_roles) k_tail_roles<false><<<(active + 31u) / 32u, 96, 0, st>>>(V, Q, it + 1u);
-                else if (bin) k_tail<true><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);
-                else k_tail<false><<<(active + 63u) / 64u, 64, 0, st>>>(V, Q, it + 1u);
+                const uint32_t spb = (uint32_t)std::max(1, std::min(32, ctx->opt_tail_slots_per_block));
+                if (ctx->opt_tail_roles && bin) k_tail_roles<true><<<(active + spb - 1u) / spb, 96, 0, gs>>>(V, Q, it + 1u, spb);
+                else if (ctx->opt_tail_roles) k_tail_roles<false><<<(active + spb - 1u) / spb, 96, 0, gs>>>(V, Q, it + 1u, spb);
+                else if (bin) k_tail<true><<<(active + 63u) / 64u, 64, 0, gs>>>(V, Q, it + 1u);
+                else k_tail<false><<<(active + 63u) / 64u, 64, 0, gs>>>(V, Q, it + 1u);
                 PTB_CUDA(ctx, mark(5));
                 PTB_CUDA(ctx, cudaGetLastError());
                 rs.launches += 1;
-                break;
+                R.done = true;
             }
         }
+        return PTB_OK;
+    };
+    for (int running = G; running > 0;)
+    {
+        running = 0;
+        for (int g = 0; g < G; ++g)
+        {
+            if (gr[g].done) continue;
+            const int rc = step_group(g);
+            if (rc != PTB_OK) return rc;
+            if (!gr[g].done) ++running;
+        }
+    }
+    for (int g = 1; g < G; ++g)  // join
+    {
+        PTB_CUDA(ctx, cudaEventRecord(rs.group_events[g], gr[g].st));
+        PTB_CUDA(ctx, cudaStreamWaitEvent(st, rs.group_events[g], 0));
     }
     k_combine<<<(rs.npix + 255) / 256, 256, 0, st>>>(V, rs.accum, ctx->second_moment ? rs.accum_sq.p : nullptr, rs.position.p, rs.id.p, sample_count);
     PTB_CUDA(ctx, mark(6));
@@ -1198,13 +1274,18 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     rs.n_class[0] += 1;
     if (prof)
     {
+        // development aid: PTB_LAUNCH_LOG=<file> lists every launch of the render (stage class, microseconds)
+        const char* log_path = std::getenv("PTB_LAUNCH_LOG");
+        std::FILE* launch_log = log_path ? std::fopen(log_path, "w") : nullptr;
         for (size_t i = 1; i < prof_used; ++i)
         {
             float d = 0;
             PTB_CUDA(ctx, cudaEventElapsedTime(&d, rs.prof_events[i - 1], rs.prof_events[i]));
             const int cls = prof_class[i];
             if (cls >= 1 && cls < 8) { rs.t_class_ms[cls] += d; rs.n_class[cls] += 1; }
+            if (launch_log) std::fprintf(launch_log, "%d %.3f\n", cls, d * 1000.0f);
         }
+        if (launch_log) std::fclose(launch_log);
     }
     return PTB_OK;
 }
@@ -1254,9 +1335,14 @@ int ptb_get_counters(ptb_context* ctx, uint64_t out[8])
     REQUIRE_DEVICE(ctx);
     if (!ctx->rs) return ctx->fail(PTB_ERR_INVALID, "no frame");
     PTB_CUDA(ctx, cudaSetDevice(ctx->device));
-    WfCounters c;
-    PTB_CUDA(ctx, cudaMemcpyAsync(&c, ctx->rs->counters.p, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
+    WfCounters cg[MAX_GROUPS], c{};
+    PTB_CUDA(ctx, cudaMemcpyAsync(cg, ctx->rs->counters.p, sizeof(cg), cudaMemcpyDeviceToHost, ctx->stream));
     PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int g = 0; g < MAX_GROUPS; ++g)  // one counter block per wavefront group; iterations: the longest group
+    {
+        c.stat_extend += cg[g].stat_extend; c.stat_shadow += cg[g].stat_shadow; c.stat_probe += cg[g].stat_probe; c.stat_paths += cg[g].stat_paths;
+        c.stat_probe_shadow += cg[g].stat_probe_shadow; c.stat_iters = std::max(c.stat_iters, cg[g].stat_iters);
+    }
     out[0] = c.stat_extend;
     out[1] = c.stat_shadow + c.stat_probe_shadow;
     out[2] = c.stat_probe;
@@ -1272,7 +1358,7 @@ int ptb_reset_counters(ptb_context* ctx)
     REQUIRE_DEVICE(ctx);
     if (!ctx->rs) return ctx->fail(PTB_ERR_INVALID, "no frame");
     PTB_CUDA(ctx, cudaSetDevice(ctx->device));
-    PTB_CUDA(ctx, cudaMemsetAsync(ctx->rs->counters.p, 0, sizeof(WfCounters), ctx->stream));
+    PTB_CUDA(ctx, cudaMemsetAsync(ctx->rs->counters.p, 0, sizeof(WfCounters) * MAX_GROUPS, ctx->stream));
     ctx->rs->launches = 0;
     ctx->rs->t_total_ms = 0;
     for (int k = 0; k < 8; ++k) { ctx->rs->t_class_ms[k] = 0; ctx->rs->n_class[k] = 0; }

@@ -318,7 +318,14 @@ PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, uint2* stack)
                     const float inv12[12] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w, i2.x, i2.y, i2.z, i2.w};
                     transform_ray_reuse(s.ray, s.ow, s.dw, s.invw, inv12);
                     s.blas_sp = s.sp;
-                    s.node = cw & ~TLAS_IDENTITY_FLAG;
+                    if (cw & TLAS_DIRECT_FLAG)
+                    {
+                        // a BLAS of one or two leaves: straight to the exact leaf tests (stage L of this very step)
+                        s.lmask = (cw >> TLAS_DIRECT_BASE_BITS) & 0xffu;
+                        s.leaf_base = cw & ((1u << TLAS_DIRECT_BASE_BITS) - 1u);
+                        s.lh = xor_permute16(s.lmask, s.ray.oi) & 0xffu;
+                    }
+                    else s.node = cw;
                 }
             }
             else s.G = e;

@@ -295,3 +295,28 @@ def test_slot_ordered_and_queue_kernels_agree(ptb, scenes, name, spp, W, H):
         assert ref[3] == v[3], f"ray counters differ for dense={k}: {ref[3]} vs {v[3]}"
         assert np.array_equal(ref[0][..., 3], v[0][..., 3])
         assert np.allclose(ref[0], v[0], rtol=1e-5, atol=1e-7), f"dense={k}: radiance differs beyond rounding"
+
+
+@pytest.mark.parametrize("name,spp,W,H", [("c2", 6, 96, 54), ("c3_small", 5, 97, 53), ("materials", 19, 33, 21)])
+def test_wavefront_groups_and_tail_layout_do_not_change_results(ptb, scenes, name, spp, W, H):
+    """`wavefront_groups` splits the slots into G independent wavefronts (own queues, counters and stream) and
+    `tail_slots_per_block` changes how the tail kernel packs the remaining slots into blocks: pure scheduling.  Slots never interact,
+    so accumulators, aux outputs and ray counts are bit-identical for every G (ragged sizes: group boundaries fall on multiples of 32
+    slots, the last group takes the remainder)."""
+    sd = _scene(scenes, name)
+    ctx = ptb.Context(0)
+    ctx.upload(sd)
+    ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
+    out = {}
+    for G, spb in ((1, 32), (2, 32), (3, 8), (8, 1)):
+        ctx.set_option("wavefront_groups", G)
+        ctx.set_option("tail_slots_per_block", spb)
+        ctx.frame_begin(W, H)
+        ctx.reset_counters()
+        ctx.render(0, spp, seed=13, max_bounces=sd.max_bounces)
+        pos, ids = ctx.read_aux()
+        c = ctx.counters()
+        out[G] = (bits(ctx.read_accum()), bits(pos), ids.copy(), (c["extend"], c["shadow"], c["probe"], c["paths"]))
+    for G, v in out.items():
+        assert all(np.array_equal(a, b) for a, b in zip(out[1][:3], v[:3])), f"wavefront_groups={G}: outputs differ"
+        assert out[1][3] == v[3], f"wavefront_groups={G}: ray counters differ"

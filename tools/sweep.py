@@ -30,7 +30,7 @@ for combo in itertools.product(*[v for _, v in axes]):
     for rep in range(2):
         ctx.frame_begin(W, H)
         ctx.reset_counters()
-        ctx.set_profiling(True)
+        ctx.set_profiling(not os.environ.get("PTB_NOPROF"))
         ctx.render(0, spp, seed=1, max_bounces=sd.max_bounces)
         t, c = ctx.timing(), ctx.counters()
         if best is None or t["render"][0] < best[0]["render"][0]:
