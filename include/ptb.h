@@ -214,13 +214,16 @@ int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active,
  *   dense_threshold   live slots per listed 32-slot group, in percent, below which the queue shade kernel takes over (default 60)
  *   shade_sort        span-local sort by shade kind in k_shade_ordered: 1, 0, < 0 automatic (scenes with >= 2 surface material kinds)
  *   sort_materials    queue shade kernel: one queue per material kind (default 1)
- *   extend_blocks, nee_blocks   resident blocks per SM (= register cap) of k_extend (5..8, default 6) / k_nee (4..8, default 5)
+ *   extend_blocks, nee_blocks   resident blocks per SM (= register cap) of k_extend (5..8, default 7) / k_nee (4..8, default 8)
  *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit 8, any-hit 12)
  *   node_quorum       lanes that must want the node stage before it runs (default 8)
  *   tail_threshold    active slots at which the wavefront loop hands the remaining slots to the single-launch tail kernel
  *                     (< 0 automatic = half the resident slot capacity of that kernel, 0 = never)
  *   tail_roles        1 (default): the tail kernel runs shadow ray, light probe and the next bounce's ray of a slot on three warps
  *                     side by side; 0: one thread per slot runs them in sequence (same results)
+ *   tail_slots_per_block   slots per three-warp block of that kernel, 1..32 (default 32; same results)
+ *   wavefront_groups  independent wavefronts per render, each over 1/G of the slots with its own queues on its own stream,
+ *                     1..8 (default 2; bit-identical results for every G; forced to 1 while profiling is on)
  *   block_threads, blocks_per_sm     launch shape of the queue shade / reference-order kernels */
 int ptb_set_option(ptb_context* ctx, const char* name, int value);
 

@@ -105,3 +105,34 @@ def test_temporal_bodies_match_oracle(po, emu, W, H):
     for f, ((ga, gv), (wa, wv)) in enumerate(zip(got, want)):
         assert same_bits_or_nan(ga, wa), f"frame {f}"
         assert same_bits_or_nan(gv, wv), f"frame {f}"
+
+
+def test_zero_component_rays_through_identity_instances(po, scenes, emu):
+    """Identity instances hand the world ray to the BLAS unchanged only when no component of origin or direction is a zero; a zero
+    takes the full arithmetic of Ray::transform (ray.rs:22-28: x*1 + y*0 + z*0 + 0 decides its sign, and with it 1/d = +-inf).
+    Axis-parallel rays with zeros of either sign, origins with zero coordinates: bit-exact against the oracle, no ties allowed for
+    the hit flag and t."""
+    sd = scenes.scene_c2()  # every instance is the identity
+    sc = po.OracleScene(sd)
+    es = emu.EmuScene(sd, po.pack_scene)
+    rng = np.random.default_rng(7)
+    n = 6000
+    o = rng.uniform(-250, 250, size=(n, 3)).astype(np.float32)
+    o[:, 1] += 50.0
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    zero = rng.integers(0, 8, size=n)  # which direction components are zeroed (never all three)
+    for k in range(3):
+        m = ((zero >> k) & 1).astype(bool) & (zero != 7)
+        d[m, k] = np.where(rng.integers(0, 2, size=m.sum()) == 1, np.float32(-0.0), np.float32(0.0))
+    d /= np.linalg.norm(d, axis=1, keepdims=True).astype(np.float32)
+    oz = rng.integers(0, 4, size=n)
+    for k in range(3):
+        m = oz == k
+        o[m, k] = np.where(rng.integers(0, 2, size=m.sum()) == 1, np.float32(-0.0), np.float32(0.0))
+    tm = np.full(n, np.inf, np.float32)
+    ref = sc.trace_closest(o, d, tm)
+    for kernel in (1, 0):
+        got = es.trace(o, d, tm, kernel=kernel)
+        compare_closest(ref, got, sc, o, d, tm, allow_ties=(kernel == 0))
+        assert np.array_equal(es.trace(o, d, tm, kernel=kernel, any_hit=True)["hit"], sc.trace_any(o, d, tm)["hit"])
+    assert ref["hit"].mean() > 0.5
