@@ -218,7 +218,7 @@ int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active,
  *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit 8, any-hit 12)
  *   node_quorum       lanes that must want the node stage before it runs (default 8)
  *   tail_threshold    active slots at which the wavefront loop hands the remaining slots to the single-launch tail kernel
- *                     (< 0 automatic = half the resident slot capacity of that kernel, 0 = never)
+ *                     (< 0 automatic = 2.5 x the resident slot capacity of that kernel, 0 = never)
  *   tail_roles        1 (default): the tail kernel runs shadow ray, light probe and the next bounce's ray of a slot on three warps
  *                     side by side; 0: one thread per slot runs them in sequence (same results)
  *   tail_slots_per_block   slots per three-warp block of that kernel, 1..32 (default 32; same results)

@@ -1142,8 +1142,10 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         else PTB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tail<false>, 64, 0));
         rs.tail_capacity = per_sm * (ctx->opt_tail_roles ? 32 : 64) * ctx->sm_count;
     }
-    // switch to the tail kernel once every remaining slot (of all groups together) fits on the device at once (0 disables, <0 = automatic)
-    const uint32_t tail_threshold = (ctx->opt_tail_threshold < 0 ? (uint32_t)rs.tail_capacity / 2u : (uint32_t)ctx->opt_tail_threshold) / (uint32_t)G;
+    // switch to the tail kernel once the remaining slots (of all groups together) are a few waves of its resident capacity (0 disables,
+    // <0 = automatic: 2.5 x capacity, the measured optimum on C3 — below it the thin wavefront iterations cost more per bounce than
+    // the tail kernel, above it the tail kernel's one-thread-per-ray throughput does)
+    const uint32_t tail_threshold = (ctx->opt_tail_threshold < 0 ? (uint32_t)rs.tail_capacity * 5u / 2u : (uint32_t)ctx->opt_tail_threshold) / (uint32_t)G;
 
     PTB_CUDA(ctx, cudaEventRecord(rs.ev_begin, st));
     PTB_CUDA(ctx, mark(-1));

@@ -158,6 +158,31 @@ PTB_HD uint32_t regen_slot(const RenderView& V, uint32_t slot)
     return regen_slot(V, slot, &o, &d);
 }
 
+// One shared, non-inlined copy of the 8-wide traversal for the per-slot bodies below (the single-launch tail kernels).  Those
+// kernels hold the whole path loop; with the traversal inlined at its four call sites they were 190 KB of code, and their few
+// resident warps — each role in a different copy — spent a third of their issue latency waiting for instructions
+// (smsp stall no_instruction 1.8 per issued instruction, profiles/r1m_c3_tail_ncu.txt).  Closest-hit or any-hit is decided at
+// run time (MODE 2); the arithmetic is the exact tier's, so results do not depend on which copy runs.
+#if defined(__CUDA_ARCH__)
+__device__ __noinline__
+#else
+inline
+#endif
+bool wide_traverse_shared(const SceneDev* S, int which, float ox, float oy, float oz, float dx, float dy, float dz, float t_max, int any, Hit* hit)
+{
+    uint2 stack[WIDE_STACK_CAP];
+    WideTrav s;
+    wide_begin(s, *S, which, ex::v3(ox, oy, oz), ex::v3(dx, dy, dz), t_max, any != 0);
+    while (wide_step<2>(s, *S, stack)) {}
+    if (s.hit_inst == TRAV_NONE) return false;
+    if (!any) { hit->t = s.t_max; hit->u = wide_hit_u(s); hit->v = wide_hit_v(s); hit->slot_or_prim = s.hit_slot; hit->inst = s.hit_inst; }
+    return true;
+}
+PTB_HD bool wide_traverse_call(const SceneDev& S, int which, V3 o, V3 d, float t_max, bool any, Hit* hit)
+{
+    return wide_traverse_shared(&S, which, o.x, o.y, o.z, d.x, d.y, d.z, t_max, any ? 1 : 0, hit);
+}
+
 // ---- extend --------------------------------------------------------------------------------------------------------------
 // returns the shade-queue kind (material kind of the hit BLAS, or Q_MISS)
 template <bool BIN>
@@ -165,7 +190,7 @@ PTB_HD uint32_t extend_ray_t(const RenderView& V, uint32_t slot, V3 o, V3 d)
 {
     Hit h;
     h.inst = 0xffffffffu;
-    const bool f = BIN ? bin_traverse<false>(V.S, 0, o, d, ex::inf(), &h) : wide_traverse<false>(V.S, 0, o, d, ex::inf(), &h);
+    const bool f = BIN ? bin_traverse<false>(V.S, 0, o, d, ex::inf(), &h) : wide_traverse_call(V.S, 0, o, d, ex::inf(), false, &h);
     if (!f)
     {
         V.hit[slot].info = 0xffffffffu;
@@ -378,7 +403,7 @@ PTB_HD void shadow_contrib_t(const RenderView& V, uint32_t slot, V3 o, float4* r
     const float4 d4 = V.shadow[slot].d;
     Hit h;
     const V3 d = ex::v3(d4.x, d4.y, d4.z);
-    const bool occluded = BIN ? bin_traverse<true>(V.S, 0, o, d, d4.w, &h) : wide_traverse<true>(V.S, 0, o, d, d4.w, &h);
+    const bool occluded = BIN ? bin_traverse<true>(V.S, 0, o, d, d4.w, &h) : wide_traverse_call(V.S, 0, o, d, d4.w, true, &h);
     if (occluded) return;
     const float4 c = V.shadow[slot].c;
     r->x += c.x; r->y += c.y; r->z += c.z;
@@ -414,11 +439,11 @@ PTB_HD uint32_t probe_contrib_t(const RenderView& V, uint32_t slot, V3 o, float4
     if (!BIN && !tlas_may_hit(V.S, 1, o, d)) return 0u;  // cannot reach the bounds of the lights (the reference-order variant always traverses)
     Hit h;
     h.inst = 0xffffffffu;
-    const bool lit = BIN ? bin_traverse<false>(V.S, 1, o, d, ex::inf(), &h) : wide_traverse<false>(V.S, 1, o, d, ex::inf(), &h);  // integrator.rs:100
+    const bool lit = BIN ? bin_traverse<false>(V.S, 1, o, d, ex::inf(), &h) : wide_traverse_call(V.S, 1, o, d, ex::inf(), false, &h);  // integrator.rs:100
     if (!lit) return 0u;
     Hit dummy;
     const float tl = h.t;
-    const bool occluded = BIN ? bin_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy) : wide_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy);  // :103
+    const bool occluded = BIN ? bin_traverse<true>(V.S, 0, o, d, tl * (1.0f - ex::EPS), &dummy) : wide_traverse_call(V.S, 0, o, d, tl * (1.0f - ex::EPS), true, &dummy);  // :103
     if (occluded) return 1u;
     const uint32_t prim = BIN ? h.slot_or_prim : V.S.tri_prim[h.slot_or_prim];
     const V3 c = probe_light_contrib(V, slot, d, tl, h.u, h.v, prim, h.inst);
