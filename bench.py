@@ -235,7 +235,7 @@ def main():
                     peak_source=peak_src, alg_bytes_per_ray=alg_ext, rays_per_launch=cn["extend"] / max(ext_launches, 1), launch_ms=ext_ms / max(ext_launches, 1),
                     grays_per_s=cn["extend"] / (ext_ms * 1e-3) / 1e9,
                     note="achieved = algorithmic bytes of the REFERENCE traversal (oracle-counted slab/triangle/instance work on its binary BVH) per second of k_extend time, not DRAM traffic: "
-                         + ("the BVH of this workload is L1/L2-resident; " if args.workload != "c4" else "") + "ncu shows k_extend issue-bound (64-70 % issue slots active, 14-15/32 lanes per instruction), see DESIGN.md §5 and profiles/",
+                         + ("the BVH of this workload is L1/L2-resident; " if args.workload != "c4" else "") + "ncu shows k_extend issue-bound (73-77 % issue slots active, 13-16/32 lanes per instruction), see DESIGN.md §5 and profiles/",
                     stage_ms={k: round(v[0] / args.steps, 3) for k, v in tm.items()},
                     shadow=dict(alg_bytes_per_ray=alg_sha, achieved=(cn["shadow"] * alg_sha / (tm["nee"][0] * 1e-3) / 1e9) if tm["nee"][0] > 0 else None,
                                 note="k_nee also traces the light probes (lights-TLAS closest hit), not counted here"))
