@@ -215,7 +215,7 @@ int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active,
  *   shade_sort        span-local sort by shade kind in k_shade_ordered: 1, 0, < 0 automatic (scenes with >= 2 surface material kinds)
  *   sort_materials    queue shade kernel: one queue per material kind (default 1)
  *   extend_blocks, nee_blocks   resident blocks per SM (= register cap) of k_extend (5..8, default 7) / k_nee (4..8, default 8)
- *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit 8, any-hit 12)
+ *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit 8, any-hit 8)
  *   node_quorum       lanes that must want the node stage before it runs (default 8)
  *   tail_threshold    active slots at which the wavefront loop hands the remaining slots to the single-launch tail kernel
  *                     (< 0 automatic = 2.5 x the resident slot capacity of that kernel, 0 = never)

@@ -82,7 +82,7 @@ struct ptb_context
     int opt_extend_kernel = 0;  // 0 wide, 1 reference-order
     int opt_block_threads = 128;
     int opt_blocks_per_sm = 8;
-    int opt_refill_below = 8, opt_nee_refill_below = 12;    // persistent kernels refill idle lanes when fewer than this many lanes of a warp are traversing
+    int opt_refill_below = 8, opt_nee_refill_below = 8;    // persistent kernels refill idle lanes when fewer than this many lanes of a warp are traversing
     int opt_node_quorum = 8;      // lanes of a warp that must want the node stage before it runs (1 = never postponed)
     int opt_extend_blocks = 7, opt_nee_blocks = 8;  // resident blocks per SM (launch bounds -> register cap) of k_extend / k_nee
     int opt_slots_per_pixel = 16;  // path slots per pixel (1..16): more slots = more paths in flight, fewer and larger wavefront iterations
