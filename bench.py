@@ -23,6 +23,7 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+OUT = sys.stdout  # main() replaces it by a private copy of the original stdout
 sys.path.insert(0, ROOT)
 
 WORKLOADS = {
@@ -100,7 +101,8 @@ def run_reference(args):
                 cpu_baseline=dict(value=v, unit="Mrays/s", cores=threads, kind="port",
                                   sample=f"{spp} spp of the {sd.width}x{sd.height} workload per step (the reference is Rust nightly + un-vendored crates: not buildable here; oracle restatement of main.rs:181-207 timed instead)"),
                 e2e=dict(value=v, unit="Mrays/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
-    print(json.dumps(line))
+    print(json.dumps(line), file=OUT)
+    OUT.flush()
 
 
 def main():
@@ -116,6 +118,12 @@ def main():
     ap.add_argument("--seed", type=int, default=20261104)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # stdout carries the ONE JSON line and nothing else: file descriptor 1 is pointed at stderr for the run (libraries write banners
+    # there, e.g. "NCCL version ..." on the first collective) and the line goes to the saved descriptor
+    global OUT
+    sys.stdout.flush()
+    OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference(args)
 
@@ -255,7 +263,8 @@ def main():
         line["roofline"] = roof
     if cpu:
         line["cpu_baseline"] = cpu
-    print(json.dumps(line))
+    print(json.dumps(line), file=OUT)
+    OUT.flush()
     if world > 1:
         dist.destroy_process_group()
 
