@@ -11,8 +11,8 @@
  *
  * Threading: one context per GPU; calls on one context must be externally serialised (the reference calls
  * the seam once per frame from the main thread, main.rs:179-219); different contexts may be driven from
- * different threads.  Kernels run on a per-context stream; ptb_render is asynchronous, ptb_read_* and
- * ptb_synchronize wait for it.
+ * different threads.  Kernels run on a per-context stream; ptb_render BLOCKS until the frame batch is done (its loop
+ * polls the device for the number of live paths); ptb_render_async runs it on a worker thread, ptb_wait joins.
  *
  * There is no CPU fallback: every compute entry point returns PTB_ERR_NO_DEVICE without a CUDA device.
  */
@@ -38,7 +38,8 @@ enum ptb_status
     PTB_ERR_NO_DEVICE = 3,   /* no CUDA device / wrong architecture */
     PTB_ERR_OOM = 4,
     PTB_ERR_NOT_BUILT = 5,   /* scene not uploaded / ptb_build not called */
-    PTB_ERR_UNSUPPORTED = 6  /* valid upstream but beyond a documented limit of this backend (e.g. > 64 media) */
+    PTB_ERR_UNSUPPORTED = 6, /* valid upstream but beyond a documented limit of this backend (e.g. > 64 media) */
+    PTB_ERR_NCCL = 7         /* NCCL error in a ptb_group_* call, see ptb_group_last_error */
 };
 
 /* Material kinds: enum Material, material.rs:80-89 (GGX split by GGXModel, material.rs:171-180). */
@@ -150,6 +151,12 @@ int ptb_rng_stream(ptb_context* ctx, uint64_t seed, uint32_t pixel, uint32_t sam
  * (shader.wgsl:63).  ptb_read_aux: `position` (first-hit point, t) and `id` ((id << 16) | first blas id) of main.rs:204-206. */
 int ptb_frame_begin(ptb_context* ctx, uint32_t width, uint32_t height);
 int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_bounces, int enable_nee);
+/* ptb_render on a worker thread of the context: returns at once; ptb_wait (or ptb_synchronize) joins it and returns its status.
+ * No other call on this context in between.  Meant for hosts that render frame after frame (main.rs:179-219) with TWO contexts on
+ * one device, alternating: the thin end of one frame's wavefront (latency-bound, device mostly idle) overlaps the dense start of
+ * the next frame on the other context. */
+int ptb_render_async(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_bounces, int enable_nee);
+int ptb_wait(ptb_context* ctx);
 int ptb_read_accum(ptb_context* ctx, float* rgba);
 int ptb_read_aux(ptb_context* ctx, float* position4, uint32_t* id);
 /* Display image of the accumulation buffer, the step after the path: rgb / w (shader.wgsl:63), Uchimura GT tonemap with the
@@ -187,16 +194,18 @@ int ptb_camera_view_projection(ptb_context* ctx, float m16[16]);
 /* Optional second moment (sum of squared sample values) for statistical parity tests; must be enabled before ptb_frame_begin. */
 int ptb_enable_second_moment(ptb_context* ctx, int enable);
 int ptb_read_second_moment(ptb_context* ctx, float* rgba);
-/* Device pointer of the accumulation buffer (W*H*4 floats) for an external collective (NCCL reduce over NVLink), and an
- * in-place `+=` from another device buffer of the same shape (used after a gather-style exchange). */
+/* Device pointer of the accumulation buffer (W*H*4 floats), e.g. for an external collective; the library's own multi-GPU
+ * path is ptb_group_* below. */
 int ptb_accum_device_ptr(ptb_context* ctx, void** dptr, size_t* bytes);
 /* Use caller-owned device memory (e.g. a torch tensor) as accumulation buffer; NULL reverts to the internal one. */
 int ptb_bind_accum(ptb_context* ctx, void* dptr, size_t bytes);
 
 /* ---- counters & timing -------------------------------------------------------------------------------------------
- * counters since the last ptb_reset_counters: [0] extend rays (world closest-hit), [1] shadow rays (world any-hit),
- * [2] light probes (lights-TLAS closest-hit), [3] paths (camera samples), [4] wavefront iterations, [5] kernel launches,
- * [6] primary rays, [7] reserved. */
+ * counters since the last ptb_reset_counters: [0] extend rays (world closest-hit) that ran a traversal, [1] shadow rays (world
+ * any-hit), [2] light probes (lights-TLAS closest-hit), [3] paths (camera samples), [4] wavefront iterations, [5] kernel
+ * launches, [6] the part of [0] traced inside the single-launch kernels (k_path / tail) instead of k_extend launches (primary
+ * rays = [3]: every path starts with one), [7] primary rays settled WITHOUT a traversal (camera outside the scene bounds, ray
+ * cannot reach them, constant background: the reference ends such a ray at its root-box test, tlas.rs:68) — not part of [0]. */
 int ptb_get_counters(ptb_context* ctx, uint64_t out[8]);
 int ptb_reset_counters(ptb_context* ctx);
 /* With profiling on, every kernel launch of ptb_render is bracketed by CUDA events on the context stream.
@@ -226,6 +235,57 @@ int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active,
  *                     1..8 (default 2; bit-identical results for every G; forced to 1 while profiling is on)
  *   block_threads, blocks_per_sm     launch shape of the queue shade / reference-order kernels */
 int ptb_set_option(ptb_context* ctx, const char* name, int value);
+
+
+/* ---- multi-GPU: sample-partitioned rendering, one NCCL reduce per frame batch ---------------------------------
+ * The frame loop main.rs:181-207 is a pure map over (pixel, sample) and the accumulation (accumulate.wgsl:23) a commutative
+ * float sum, so a frame batch shards by GLOBAL SAMPLE INDEX: every GPU holds the full scene and renders a contiguous block of the
+ * batch's samples for all pixels; RNG streams are keyed by (seed, pixel, global sample index), so the union of the samples is
+ * the same set for every group size.  One collective per batch: ncclReduce(sum, float32, W*H*4) of the accumulation buffers
+ * onto the root over NVLink, called from this library (libptb.so links libnccl).
+ *
+ * Two ways to form a group:
+ *   ptb_group_create   ONE process drives n devices (what a Rust host replacing main.rs:179-219 would use): the group owns one
+ *                      context per device (ptb_group_context) and runs the members on its own host threads.
+ *   ptb_group_join     one process per GPU (torchrun / MPI launchers): every rank passes its own context and the 128-byte id
+ *                      that rank 0 obtained from ptb_group_unique_id (the host ships it to the other ranks by any means).
+ * Group members are numbered 0..n_ranks-1 (create: the position in device_ordinals; join: the rank).
+ * Scene, camera and frame size are per-context state: set them on every member (ptb_group_context) or with the broadcast
+ * helpers below, which apply one call to every LOCAL member in parallel. */
+typedef struct ptb_group ptb_group;
+int ptb_group_create(int n_devices, const int* device_ordinals, ptb_group** out);
+int ptb_group_unique_id(uint8_t id[128]);
+int ptb_group_join(ptb_context* ctx, int n_ranks, int rank, const uint8_t id[128], ptb_group** out);
+/* Frees the communicators; contexts made by ptb_group_create are destroyed, a joined context stays the caller's. */
+void ptb_group_destroy(ptb_group* g);
+const char* ptb_group_last_error(const ptb_group* g);
+int ptb_group_size(const ptb_group* g, int* n_local, int* n_ranks);
+ptb_context* ptb_group_context(ptb_group* g, int local_index);
+/* Block of the global sample range [begin, begin + count) owned by `rank` of `n_ranks`: contiguous, the first count % n_ranks
+ * ranks get one sample more (count may come out 0).  Pure host arithmetic, usable without a device. */
+int ptb_group_sample_range(uint32_t begin, uint32_t count, int rank, int n_ranks, uint32_t* first, uint32_t* mine);
+/* Broadcast helpers: the ptb_* call of the same name on every local member (in parallel; first failure is returned). */
+int ptb_group_scene_upload(ptb_group* g, const float* verts, uint64_t ntri, const ptb_blas_desc* blas, uint32_t nblas, const ptb_instance* inst, uint32_t ninst);
+int ptb_group_build(ptb_group* g);
+int ptb_group_set_camera(ptb_group* g, const float origin[3], const float target[3], float fov_deg, float aspect_ratio);
+int ptb_group_set_option(ptb_group* g, const char* name, int value);
+int ptb_group_frame_begin(ptb_group* g, uint32_t width, uint32_t height);
+/* Renders the samples [sample_begin, sample_begin + sample_count) of every pixel, partitioned over the ranks with
+ * ptb_group_sample_range; every member adds its block into its own accumulation buffer (ptb_render).  Blocks until the local
+ * members have finished. */
+int ptb_group_render(ptb_group* g, uint32_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_bounces, int enable_nee);
+/* Sums the accumulation buffers of all ranks onto `root` in place (one ncclReduce per member, on the member's stream; collective:
+ * every rank must call it).  Afterwards the root's buffer holds the whole batch (w = sample_count); the other members hold their
+ * partial sums until the next ptb_group_frame_begin.  position / id come from the root's own samples. */
+int ptb_group_reduce(ptb_group* g, int root);
+/* ptb_read_accum / ptb_read_aux of member `root` when it is local to this process, PTB_ERR_INVALID otherwise. */
+int ptb_group_read_accum(ptb_group* g, int root, float* rgba);
+int ptb_group_read_aux(ptb_group* g, int root, float* position4, uint32_t* id);
+/* Sum of ptb_get_counters over the local members (iterations: the maximum). */
+int ptb_group_get_counters(ptb_group* g, uint64_t out[8]);
+int ptb_group_reset_counters(ptb_group* g);
+/* Device time of the last ptb_group_reduce on the first local member, in milliseconds (CUDA events on its stream). */
+int ptb_group_reduce_ms(ptb_group* g, float* ms);
 
 #ifdef __cplusplus
 }

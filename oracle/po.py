@@ -36,22 +36,48 @@ def build(force=False):
     return so
 
 
+BUILD_FLAGS = "-O2 -march=x86-64-v3 -ffp-contract=off (portable checker build)"
+
+
+def use_native_build():
+    """bench.py's CPU arms only: compile the oracle on THIS host with the reference's release settings (-O3, LTO, native CPU;
+    oracle/Makefile `native`) and load that instead of the portable checker build.  Must be called before the first lib().
+    Falls back to the portable build (and says so in BUILD_FLAGS) when the compiler is missing or the build fails."""
+    global _LIB, BUILD_FLAGS
+    if _LIB is not None:
+        return BUILD_FLAGS
+    so = os.path.join(_HERE, "_native", "libpt_oracle_native.so")
+    try:
+        subprocess.check_call(["make", "-C", _HERE, "-s", "native"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        _LIB = C.CDLL(so)
+        _declare(_LIB)
+        BUILD_FLAGS = "-O3 -march=native -ffp-contract=off, one translation unit, built on this host (reference: opt-level 3, thin LTO, target-cpu=native; Cargo.toml:10-11, .cargo/config.toml:1-2)"
+    except Exception as e:  # noqa: BLE001
+        _LIB = None
+        BUILD_FLAGS += f"; native build unavailable: {type(e).__name__}"
+    return BUILD_FLAGS
+
+
+def _declare(L):
+    L.po_last_error.restype = C.c_char_p
+    L.po_scene_create.restype = C.c_void_p
+    L.po_scene_create.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
+    L.po_scene_destroy.argtypes = [C.c_void_p]
+    L.po_render.restype = C.c_double
+    L.po_generate_blas_span.restype = C.c_uint32
+    L.po_light_count.restype = C.c_uint32
+    L.po_light_count.argtypes = [C.c_void_p]
+    L.po_default_threads.restype = C.c_int
+    for f in ("po_lk_hash", "po_low_bias_hash", "po_scramble_base2"):
+        getattr(L, f).restype = C.c_uint32
+
+
 def lib():
     global _LIB
     if _LIB is None:
         _LIB = C.CDLL(build())
-        L = _LIB
-        L.po_last_error.restype = C.c_char_p
-        L.po_scene_create.restype = C.c_void_p
-        L.po_scene_create.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
-        L.po_scene_destroy.argtypes = [C.c_void_p]
-        L.po_render.restype = C.c_double
-        L.po_generate_blas_span.restype = C.c_uint32
-        L.po_light_count.restype = C.c_uint32
-        L.po_light_count.argtypes = [C.c_void_p]
-        L.po_default_threads.restype = C.c_int
-        for f in ("po_lk_hash", "po_low_bias_hash", "po_scramble_base2"):
-            getattr(L, f).restype = C.c_uint32
+        _declare(_LIB)
+        return _LIB
     return _LIB
 
 

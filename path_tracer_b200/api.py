@@ -18,19 +18,25 @@ from . import scenes as _scenes
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
-PTB_OK, PTB_ERR_INVALID, PTB_ERR_CUDA, PTB_ERR_NO_DEVICE, PTB_ERR_OOM, PTB_ERR_NOT_BUILT, PTB_ERR_UNSUPPORTED = range(7)
-_STATUS = {1: "PTB_ERR_INVALID", 2: "PTB_ERR_CUDA", 3: "PTB_ERR_NO_DEVICE", 4: "PTB_ERR_OOM", 5: "PTB_ERR_NOT_BUILT", 6: "PTB_ERR_UNSUPPORTED"}
+PTB_OK, PTB_ERR_INVALID, PTB_ERR_CUDA, PTB_ERR_NO_DEVICE, PTB_ERR_OOM, PTB_ERR_NOT_BUILT, PTB_ERR_UNSUPPORTED, PTB_ERR_NCCL = range(8)
+_STATUS = {1: "PTB_ERR_INVALID", 2: "PTB_ERR_CUDA", 3: "PTB_ERR_NO_DEVICE", 4: "PTB_ERR_OOM", 5: "PTB_ERR_NOT_BUILT", 6: "PTB_ERR_UNSUPPORTED", 7: "PTB_ERR_NCCL"}
 
 EXPORTS = [
     "ptb_abi_version", "ptb_create", "ptb_destroy", "ptb_last_error", "ptb_synchronize", "ptb_scene_upload", "ptb_scene_set_env", "ptb_build",
     "ptb_set_build_threads", "ptb_bvh_blas_counts", "ptb_bvh_blas_nodes", "ptb_bvh_blas_triangles", "ptb_bvh_tlas_counts", "ptb_bvh_tlas_nodes",
     "ptb_light_count", "ptb_light_sampler", "ptb_bvh_stats", "ptb_trace_closest", "ptb_trace_any", "ptb_trace_upload", "ptb_trace_resident",
-    "ptb_trace_download", "ptb_set_camera", "ptb_camera_rays", "ptb_ss_sobol", "ptb_rng_stream", "ptb_frame_begin", "ptb_render", "ptb_read_accum",
+    "ptb_trace_download", "ptb_set_camera", "ptb_camera_rays", "ptb_ss_sobol", "ptb_rng_stream", "ptb_frame_begin", "ptb_render", "ptb_render_async", "ptb_wait", "ptb_read_accum",
     "ptb_read_aux", "ptb_read_rgb8", "ptb_enable_second_moment", "ptb_read_second_moment", "ptb_accum_device_ptr", "ptb_bind_accum", "ptb_get_counters",
     "ptb_reset_counters", "ptb_set_profiling", "ptb_get_timing", "ptb_get_iteration_log", "ptb_set_option",
     "ptb_state_reset", "ptb_state_update", "ptb_state_update_resident", "ptb_state_read", "ptb_state_read_rgb8", "ptb_state_device_ptr", "ptb_state_timing", "ptb_frame_next",
     "ptb_camera_view_projection",
+    "ptb_group_create", "ptb_group_unique_id", "ptb_group_join", "ptb_group_destroy", "ptb_group_last_error", "ptb_group_size", "ptb_group_context",
+    "ptb_group_sample_range", "ptb_group_scene_upload", "ptb_group_build", "ptb_group_set_camera", "ptb_group_set_option", "ptb_group_frame_begin",
+    "ptb_group_render", "ptb_group_reduce", "ptb_group_read_accum", "ptb_group_read_aux", "ptb_group_get_counters", "ptb_group_reset_counters",
+    "ptb_group_reduce_ms",
 ]
+# ptb_get_counters: [0] extend rays that ran a traversal, [7] primary rays settled by the bounds pre-test without one (k_extend)
+COUNTER_NAMES = ["extend", "shadow", "probe", "paths", "iterations", "launches", "extend_path", "settled"]
 
 
 class PtbError(RuntimeError):
@@ -56,6 +62,26 @@ def lib_path():
     return os.path.join(_HERE, "libptb.so")
 
 
+def _preload_nccl():
+    """libptb.so links libnccl.so.2 (ptb_group_*).  PyTorch ships its own, newer libnccl.so.2 under the same SONAME: whichever is
+    loaded first serves both, and torch fails to import on top of the older system library.  So in a Python process the copy
+    bundled with torch is loaded first when there is one; a host without Python resolves the system library as usual."""
+    import importlib.util
+    try:
+        spec = importlib.util.find_spec("nvidia")
+    except (ImportError, ValueError):
+        spec = None
+    for base in (spec.submodule_search_locations if spec and spec.submodule_search_locations else []):
+        cand = os.path.join(base, "nccl", "lib", "libnccl.so.2")
+        if os.path.exists(cand):
+            try:
+                C.CDLL(cand, mode=C.RTLD_GLOBAL)
+                return cand
+            except OSError:
+                pass
+    return None
+
+
 def lib():
     """Load libptb.so.  Fails loudly when the CUDA extension has not been built (no fallback)."""
     global _LIB
@@ -63,6 +89,7 @@ def lib():
         p = lib_path()
         if not os.path.exists(p):
             raise ImportError(f"{p} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` (make -C path_tracer_b200/csrc)")
+        _preload_nccl()
         L = C.CDLL(p)
         L.ptb_last_error.restype = C.c_char_p
         L.ptb_last_error.argtypes = [C.c_void_p]
@@ -109,10 +136,23 @@ class Context:
         self.h = h
         self.device = device
         self.width = self.height = 0
+        self._owned = True
+
+    @classmethod
+    def borrow(cls, handle, device):
+        """View of a ptb_context owned by someone else (a member of a ptb_group): never destroyed from here."""
+        self = cls.__new__(cls)
+        self.L = lib()
+        self.h = C.c_void_p(handle)
+        self.device = device
+        self.width = self.height = 0
+        self._owned = False
+        return self
 
     def close(self):
         if getattr(self, "h", None):
-            self.L.ptb_destroy(self.h)
+            if self._owned:
+                self.L.ptb_destroy(self.h)
             self.h = None
 
     def __del__(self):
@@ -247,6 +287,13 @@ class Context:
     def render(self, sample_begin, sample_count, seed=1, max_bounces=1024, enable_nee=True):
         self._ck(self.L.ptb_render(self.h, sample_begin, sample_count, C.c_uint64(seed), max_bounces, int(enable_nee)))
 
+    def render_async(self, sample_begin, sample_count, seed=1, max_bounces=1024, enable_nee=True):
+        """ptb_render on a worker thread of the context; wait() joins it.  For two contexts on one device rendering alternate frames."""
+        self._ck(self.L.ptb_render_async(self.h, sample_begin, sample_count, C.c_uint64(seed), max_bounces, int(enable_nee)))
+
+    def wait(self):
+        self._ck(self.L.ptb_wait(self.h))
+
     def read_accum(self, out=None):
         if out is None:
             out = np.zeros((self.height, self.width, 4), np.float32)
@@ -340,8 +387,9 @@ class Context:
     def counters(self):
         out = np.zeros(8, np.uint64)
         self._ck(self.L.ptb_get_counters(self.h, _p(out)))
-        names = ["extend", "shadow", "probe", "paths", "iterations", "launches", "primary", "reserved"]
-        return {k: int(v) for k, v in zip(names, out)}
+        d = {k: int(v) for k, v in zip(COUNTER_NAMES, out)}
+        d["primary"] = d["paths"]  # every path starts with exactly one primary ray
+        return d
 
     def reset_counters(self):
         self._ck(self.L.ptb_reset_counters(self.h))

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "host_scene.h"
@@ -93,11 +94,28 @@ struct ptb_context
     int opt_tail_roles = 1;       // tail kernel with shadow / probe / next-bounce traversals on three warps side by side (0: one thread per slot)
     int opt_tail_slots_per_block = 32;  // k_tail_roles: slots per block of three warps (1..32)
     int opt_tail_threshold = -1;  // active slots at which ptb_render switches to the tail kernel (<0 automatic, 0 never)
+    int opt_path_threshold = 0;   // active slots at which ptb_render hands ALL remaining slots to the persistent path kernel k_path (0 = never, the default: measured slower than thin iterations + tail kernel; <0 automatic)
+    int opt_path_blocks = 5;      // resident blocks per SM (register cap) of k_path (4..6)
+    int opt_shared_device = 0;    // 1: another context renders on this device at the same time (ptb_render_async pairs): leave it room, see sized_grid in render.cu
+    int opt_thin_rays_per_lane = 0;  // > 0: persistent kernels take only ceil(live / (128 * this)) blocks once that is fewer than their full grid
+    int opt_finish_quorum = 8;    // k_path: lanes with a finished traversal that make the warp leave the stepping loop and shade
     int profiling = 0;
     int second_moment = 0;
 
     ptb::RenderState* rs = nullptr;
     ptb::TemporalState* ts = nullptr;
+
+    // ptb_render_async: the blocking render loop on a worker thread of this context (joined by ptb_wait / ptb_synchronize / ptb_destroy)
+    std::thread* async_thread = nullptr;
+    int async_rc = 0;
+    int wait_async()
+    {
+        if (!async_thread) return 0;
+        async_thread->join();
+        delete async_thread;
+        async_thread = nullptr;
+        return async_rc;
+    }
 
     int fail(int code, const std::string& m)
     {

@@ -10,13 +10,16 @@
 //   bool start(uint32_t index, WideTrav& tr)   fetch work item `index`, call wide_begin; false = the item needs no traversal
 //   bool finish(WideTrav& tr, bool mine)       called by ALL lanes of the warp together; `mine` = this lane's traversal just
 //                                              ended.  May begin a follow-up traversal for the lane (return true).
+// `finish_quorum` (jobs whose finish() is expensive — k_path shades in it): the stepping loop also ends, and finish() runs, as
+// soon as that many lanes are waiting with a finished traversal — or a quarter of the warp's live lanes, whichever is smaller, so
+// that a warp down to a few long paths does not make a finished lane wait for the others.  Compiled in only with GATED.
 #pragma once
 #include "traverse.h"
 
 namespace ptb {
 
-template <int MODE, class Job>
-__device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, uint32_t* cursor, uint32_t total, int refill_below, int node_quorum)
+template <int MODE, class Job, bool GATED = false>
+__device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, uint32_t* cursor, uint32_t total, int refill_below, int node_quorum, int finish_quorum = 33)
 {
     uint2 stack[WIDE_STACK_CAP];
     WideTrav tr;
@@ -70,6 +73,7 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, ui
             continue;
         }
         const int keep = more ? refill_below : 1;
+        unsigned done = 0u;
         do
         {
             if (state == 1 && !wide_step_pop(tr, S, stack)) state = 2;
@@ -79,7 +83,8 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, ui
             const bool allow = __popc(wn) >= node_quorum || wl == 0u;
             if (state == 1 && !wide_step_work<MODE>(tr, S, stack, allow)) state = 2;
             busy = __ballot_sync(FULL, state == 1);
-        } while (__popc(busy) >= keep);
+            if constexpr (GATED) done = __ballot_sync(FULL, state == 2);
+        } while (__popc(busy) >= keep && (!GATED || __popc(done) < min(finish_quorum, (__popc(busy | done) + 3) >> 2)));
     }
 }
 

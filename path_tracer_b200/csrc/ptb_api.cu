@@ -76,6 +76,7 @@ static void free_device(ptb_context* c)
 void ptb_destroy(ptb_context* ctx)
 {
     if (!ctx) return;
+    ctx->wait_async();
     if (!ctx->host_only)
     {
         cudaSetDevice(ctx->device);
@@ -93,8 +94,9 @@ const char* ptb_last_error(const ptb_context* ctx) { return ctx ? ctx->err.c_str
 int ptb_synchronize(ptb_context* ctx)
 {
     REQUIRE_DEVICE(ctx);
+    const int rc = ctx->wait_async();
     PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return PTB_OK;
+    return rc;
 }
 
 int ptb_set_build_threads(ptb_context* ctx, int threads)
@@ -434,6 +436,11 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "slots_per_pixel") ctx->opt_slots_per_pixel = value;
     else if (n == "tail_threshold") ctx->opt_tail_threshold = value;
     else if (n == "tail_roles") ctx->opt_tail_roles = value;
+    else if (n == "path_threshold") ctx->opt_path_threshold = value;
+    else if (n == "shared_device") ctx->opt_shared_device = value ? 1 : 0;
+    else if (n == "thin_rays_per_lane") ctx->opt_thin_rays_per_lane = std::max(0, value);
+    else if (n == "path_blocks") ctx->opt_path_blocks = std::max(4, std::min(6, value));
+    else if (n == "finish_quorum") ctx->opt_finish_quorum = std::max(1, std::min(32, value));
     else if (n == "tail_slots_per_block") ctx->opt_tail_slots_per_block = value;
     else if (n == "wide_collapse") ctx->scene.wide_collapse = value;  // takes effect at the next ptb_build
     else if (n == "dense") ctx->opt_dense = value;

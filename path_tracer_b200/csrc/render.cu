@@ -36,7 +36,7 @@ struct WfSet  // 64 B
 struct WfCounters
 {
     WfSet set[3];
-    unsigned long long stat_extend, stat_shadow, stat_probe, stat_paths, stat_iters, stat_probe_shadow;
+    unsigned long long stat_extend, stat_shadow, stat_probe, stat_paths, stat_iters, stat_probe_shadow, stat_settled, stat_extend_path;
 };
 
 struct Queues
@@ -55,6 +55,7 @@ struct Queues
 
 constexpr uint32_t POLL_RING = 8192;
 constexpr int MAX_GROUPS = 8;  // independent wavefronts per render (wavefront_groups), each on its own stream
+constexpr uint32_t PATH_AUTO_PER_LANE = 8;  // automatic path_threshold: live slots per resident lane of k_path at which it takes over
 
 struct RenderState
 {
@@ -258,7 +259,7 @@ __global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint
     persistent_trace<0>(V.S, job, &S.cur_extend, n_cont + n_term, refill_below, node_quorum);
     const unsigned long long p = warp_sum(job.paths), q = warp_sum(job.settled);
     if ((threadIdx.x & 31u) == 0u && p) atomicAdd(&Q.c->stat_paths, p);
-    if ((threadIdx.x & 31u) == 0u && q) atomicAdd(&Q.c->stat_extend, q);  // primary rays settled in start(): rays nonetheless
+    if ((threadIdx.x & 31u) == 0u && q) atomicAdd(&Q.c->stat_settled, q);  // primary rays settled in start() without a traversal: counted apart
 }
 
 // reference-order variant (binary trees, reference visit order): static chunks of 32, one ray per lane
@@ -430,6 +431,158 @@ __global__ void __launch_bounds__(128, MB) k_nee(RenderView V, Queues Q, uint32_
         if (a) atomicAdd(&Q.c->stat_shadow, a);
         if (b) atomicAdd(&Q.c->stat_probe, b);
         if (c) atomicAdd(&Q.c->stat_probe_shadow, c);
+    }
+}
+
+// ---- path: every remaining slot run to completion in ONE persistent launch -----------------------------------------------------
+// Once the wavefront has thinned out (C3: from iteration ~17 on, 8 % of the frame's rays spread over 130 further iterations and
+// a tail of 1024-bounce paths) every launch of the three-kernel iteration is floored by the latency of its slowest
+// ray — 110-130 us per kernel however few rays it holds (profiles/r1l_c3_launch_log.txt) — and the frame pays that floor ~400
+// times.  k_path replaces all of those launches and the tail kernel: a lane keeps its slot through extend -> shade -> shadow ray ->
+// light probe -> probe visibility -> next bounce -> ... -> regeneration of the slot's next sample, as a chain of follow-up
+// traversals in the persistent loop of persist.cuh (finish() of one traversal begins the next), and takes another slot from the
+// cont / term queues of the switch-over iteration only when its slot has run out of samples.  The traversal is the one shared
+// state machine (MODE 2: closest / any hit decided per lane), so lanes tracing primary, shadow and probe rays re-converge at every
+// stage.  Shading runs inside finish(), gated by `finish_quorum` so that it executes with several lanes at a time.
+// Per-slot arithmetic and its order (shade_slot, the NEE sum of nee_slot_t, regen_slot) are those of the wavefront kernels.
+struct PathJob
+{
+    const RenderView& V;
+    const Queues& Q;
+    uint32_t b, n_cont;
+    uint32_t slot = 0, flags = 0, stage = 0;  // stage: 0 extend, 1 shadow, 2 probe (lights TLAS), 3 probe visibility
+    V3 o;
+    float4 r;
+    float lt = 0, lu = 0, lv = 0;
+    uint32_t lslot = 0, linst = 0;
+    unsigned long long n_ext = 0, n_shadow = 0, n_probe = 0, n_probe_shadow = 0, paths = 0, settled = 0;
+
+    // regenerate the slot (finalise + accumulate the finished sample, raygen the next) and begin its primary ray; false: out of samples
+    __device__ __forceinline__ bool begin_sample(WideTrav& tr)
+    {
+        V3 ro, rd;
+        for (;;)
+        {
+            if (!(regen_slot(V, slot, &ro, &rd) & WF_NEXT)) { Q.state[slot] = 0u; return false; }
+            ++paths;
+            if (V.S.env != nullptr || tlas_may_hit(V.S, 0, ro, rd)) break;
+            V.path[slot].radiance = f4(0.006f, 0.006f, 0.006f, 0.0f);  // background path settled without a traversal (as ExtendJob::start)
+            ++settled;
+        }
+        wide_begin(tr, V.S, 0, ro, rd, ex::inf(), false);
+        stage = 0;
+        return true;
+    }
+    __device__ __forceinline__ bool begin_bounce(WideTrav& tr)
+    {
+        if (flags & WF_NEXT)
+        {
+            const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
+            wide_begin(tr, V.S, 0, ex::v3(o4.x, o4.y, o4.z), ex::v3(d4.x, d4.y, d4.z), ex::inf(), false);
+            stage = 0;
+            return true;
+        }
+        return begin_sample(tr);
+    }
+    __device__ __forceinline__ bool begin_probe(WideTrav& tr)
+    {
+        const float4 d4 = V.probe[slot].d;
+        const V3 d = ex::v3(d4.x, d4.y, d4.z);
+        ++n_probe;
+        if (!tlas_may_hit(V.S, 1, o, d)) return false;
+        wide_begin(tr, V.S, 1, o, d, ex::inf(), false);
+        stage = 2;
+        return true;
+    }
+    __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
+    {
+        if (idx < n_cont)
+        {
+            slot = Q.cont[b][idx];
+            flags = WF_NEXT;
+            return begin_bounce(tr);
+        }
+        slot = Q.term[b][idx - n_cont];
+        return begin_sample(tr);
+    }
+    __device__ __forceinline__ bool finish(WideTrav& tr, bool mine)
+    {
+        if (!mine) return false;
+        if (stage == 0)
+        {
+            ++n_ext;
+            if (tr.hit_inst == TRAV_NONE) V.hit[slot].info = 0xffffffffu;
+            else
+            {
+                const uint32_t prim = V.S.tri_prim[tr.hit_slot];
+                V3 n;
+                bool ff;
+                finish_hit(V.S, tr.dw, tr.hit_inst, prim, wide_hit_u(tr), wide_hit_v(tr), &n, &ff);
+                V.hit[slot].tn = f4(tr.t_max, n.x, n.y, n.z);
+                V.hit[slot].info = tr.hit_inst | (ff ? 0x80000000u : 0u);
+            }
+            flags = shade_slot(V, slot);
+            n_probe += (flags & WF_PROBE_OUT) ? 1u : 0u;
+            if (!(flags & (WF_SHADOW | WF_PROBE))) return begin_bounce(tr);
+            const float4 o4 = V.ray[slot].o;
+            o = ex::v3(o4.x, o4.y, o4.z);
+            r = V.path[slot].radiance;
+            if (flags & WF_SHADOW)
+            {
+                const float4 d4 = V.shadow[slot].d;
+                wide_begin(tr, V.S, 0, o, ex::v3(d4.x, d4.y, d4.z), d4.w, true);
+                stage = 1;
+                ++n_shadow;
+                return true;
+            }
+            if (begin_probe(tr)) return true;
+        }
+        else if (stage == 1)
+        {
+            if (tr.hit_inst == TRAV_NONE)
+            {
+                const float4 c = V.shadow[slot].c;
+                r.x += c.x; r.y += c.y; r.z += c.z;
+            }
+            if ((flags & WF_PROBE) && begin_probe(tr)) return true;
+        }
+        else if (stage == 2)
+        {
+            if (tr.hit_inst != TRAV_NONE)
+            {
+                lt = tr.t_max; lu = wide_hit_u(tr); lv = wide_hit_v(tr); lslot = tr.hit_slot; linst = tr.hit_inst;
+                wide_begin(tr, V.S, 0, o, tr.dw, lt * (1.0f - ex::EPS), true);
+                stage = 3;
+                ++n_probe_shadow;
+                return true;
+            }
+        }
+        else if (tr.hit_inst == TRAV_NONE)
+        {
+            const V3 c = probe_light_contrib(V, slot, tr.dw, lt, lu, lv, V.S.tri_prim[lslot], linst);
+            r.x += c.x; r.y += c.y; r.z += c.z;
+        }
+        V.path[slot].radiance = r;  // both estimates of the bounce added in nee_slot_t's order
+        return begin_bounce(tr);
+    }
+};
+
+template <int MB>
+__global__ void __launch_bounds__(128, MB) k_path(RenderView V, Queues Q, uint32_t it, int refill_below, int node_quorum, int finish_quorum)
+{
+    WfSet& S = Q.c->set[it % 3u];
+    PathJob job{V, Q, it & 1u, S.n_cont};
+    persistent_trace<2, PathJob, true>(V.S, job, &S.cur_extend, S.n_cont + S.n_term, refill_below, node_quorum, finish_quorum);
+    const unsigned long long a = warp_sum(job.n_ext), b = warp_sum(job.n_shadow), c = warp_sum(job.n_probe), d = warp_sum(job.n_probe_shadow), e = warp_sum(job.paths),
+                             f = warp_sum(job.settled);
+    if ((threadIdx.x & 31u) == 0u)
+    {
+        if (a) { atomicAdd(&Q.c->stat_extend, a); atomicAdd(&Q.c->stat_extend_path, a); }
+        if (b) atomicAdd(&Q.c->stat_shadow, b);
+        if (c) atomicAdd(&Q.c->stat_probe, c);
+        if (d) atomicAdd(&Q.c->stat_probe_shadow, d);
+        if (e) atomicAdd(&Q.c->stat_paths, e);
+        if (f) atomicAdd(&Q.c->stat_settled, f);
     }
 }
 
@@ -684,6 +837,7 @@ __global__ void __launch_bounds__(64) k_tail(RenderView V, Queues Q, uint32_t it
     if (n_ext | n_paths)
     {
         atomicAdd(&Q.c->stat_extend, n_ext);
+        atomicAdd(&Q.c->stat_extend_path, n_ext);
         atomicAdd(&Q.c->stat_shadow, n_sh);
         atomicAdd(&Q.c->stat_probe, n_pr);
         atomicAdd(&Q.c->stat_probe_shadow, n_ps);
@@ -791,7 +945,7 @@ __global__ void __launch_bounds__(96) k_tail_roles(RenderView V, Queues Q, uint3
     }
     if (n_ext | n_paths | n_sh | n_pr)
     {
-        if (n_ext) atomicAdd(&Q.c->stat_extend, n_ext);
+        if (n_ext) { atomicAdd(&Q.c->stat_extend, n_ext); atomicAdd(&Q.c->stat_extend_path, n_ext); }
         if (n_sh) atomicAdd(&Q.c->stat_shadow, n_sh);
         if (n_pr) atomicAdd(&Q.c->stat_probe, n_pr);
         if (n_ps) atomicAdd(&Q.c->stat_probe_shadow, n_ps);
@@ -1098,6 +1252,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         bool dense = false, done = false;
         uint32_t* h_flags = nullptr;
         uint32_t tail_threshold = 0;
+        uint32_t bound = 0;  // upper bound of the group's live slots (the last polled count; live counts never grow)
     };
     GroupRun gr[MAX_GROUPS];
     for (int g = 0; g < G; ++g)
@@ -1146,6 +1301,11 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     // <0 = automatic: 2.5 x capacity, the measured optimum on C3 — below it the thin wavefront iterations cost more per bounce than
     // the tail kernel, above it the tail kernel's one-thread-per-ray throughput does)
     const uint32_t tail_threshold = (ctx->opt_tail_threshold < 0 ? (uint32_t)rs.tail_capacity * 5u / 2u : (uint32_t)ctx->opt_tail_threshold) / (uint32_t)G;
+    // The persistent path kernel takes over earlier and replaces thin iterations and tail alike (wide kernels only): once the live
+    // slots are down to a few rays per resident lane, a three-kernel iteration costs its latency floor, not its work (automatic:
+    // PATH_AUTO_PER_LANE slots per lane of the k_path grid, see DESIGN.md for the sweep)
+    const uint32_t path_lanes = (uint32_t)(ctx->sm_count * ctx->opt_path_blocks * threads);
+    const uint32_t path_threshold = bin ? 0u : (ctx->opt_path_threshold < 0 ? path_lanes * PATH_AUTO_PER_LANE : (uint32_t)ctx->opt_path_threshold) / (uint32_t)G;
 
     PTB_CUDA(ctx, cudaEventRecord(rs.ev_begin, st));
     PTB_CUDA(ctx, mark(-1));
@@ -1172,6 +1332,36 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     }
     for (int g = 0; g < G; ++g) gr[g].dense = !bin && ctx->opt_dense != 0;
 
+    // Grid of a persistent traversal / queue kernel compiled for `blocks` resident blocks per SM, given an upper bound of the work items.
+    // shared_device = 1 (two contexts rendering alternate frames on one device, ptb_render_async): the dense launches leave one block
+    // slot per SM free and the thin ones take only the blocks their work fills at thin_rays_per_lane items per lane, so the other
+    // context's kernels become resident at once instead of at this context's next launch boundary.
+    auto sized_grid = [&](int blocks, uint32_t bound) -> int {
+        int per_sm = blocks;
+        if (ctx->opt_shared_device && per_sm > 1) per_sm -= 1;
+        int g = ctx->sm_count * per_sm;
+        if (ctx->opt_thin_rays_per_lane > 0)
+        {
+            const uint64_t per_block = (uint64_t)threads * (uint64_t)ctx->opt_thin_rays_per_lane;
+            g = (int)std::min<uint64_t>((uint64_t)g, std::max<uint64_t>(1u, ((uint64_t)bound + per_block - 1u) / per_block));
+        }
+        return g;
+    };
+    for (int g = 0; g < G; ++g) gr[g].bound = gr[g].Q.npix;
+    auto launch_path = [&](int g, uint32_t it) -> int {
+        const int pg = ctx->sm_count * ctx->opt_path_blocks, fq = ctx->opt_finish_quorum, rb = ctx->opt_refill_below, nq = ctx->opt_node_quorum;
+        switch (ctx->opt_path_blocks)
+        {
+        case 4: k_path<4><<<pg, threads, 0, gr[g].st>>>(V, gr[g].Q, it, rb, nq, fq); break;
+        case 6: k_path<6><<<pg, threads, 0, gr[g].st>>>(V, gr[g].Q, it, rb, nq, fq); break;
+        default: k_path<5><<<ctx->sm_count * 5, threads, 0, gr[g].st>>>(V, gr[g].Q, it, rb, nq, fq); break;
+        }
+        PTB_CUDA(ctx, mark(5));
+        PTB_CUDA(ctx, cudaGetLastError());
+        rs.launches += 1;
+        gr[g].done = true;
+        return PTB_OK;
+    };
     // one wavefront iteration of group g (three launches on its stream) and its poll; sets done when the group has finished
     auto step_group = [&](int g) -> int {
         GroupRun& R = gr[g];
@@ -1183,19 +1373,21 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         if (bin) k_extend_bin<<<grid, threads, 0, gs>>>(V, Q, it);
         else
         {
-            const int eg = ctx->sm_count * ctx->opt_extend_blocks, so = dense ? -1 : (sort ? 1 : 0);
-            switch (ctx->opt_extend_blocks)
+            const int so = dense ? -1 : (sort ? 1 : 0);
+            const int eb = (ctx->opt_extend_blocks == 5 || ctx->opt_extend_blocks == 7 || ctx->opt_extend_blocks == 8) ? ctx->opt_extend_blocks : 6;
+            const int eg = sized_grid(eb, R.bound);
+            switch (eb)
             {
             case 5: k_extend<5><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
             case 7: k_extend<7><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
             case 8: k_extend<8><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
-            default: k_extend<6><<<ctx->sm_count * 6, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
+            default: k_extend<6><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
             }
         }
         PTB_CUDA(ctx, mark(2));
         if (dense && shade_sort) k_shade_ordered<true><<<shade_grid, 256, 0, gs>>>(V, Q, it);
         else if (dense) k_shade_ordered<false><<<shade_grid, 256, 0, gs>>>(V, Q, it);
-        else k_shade<<<grid, threads, 0, gs>>>(V, Q, it);
+        else k_shade<<<sized_grid(std::max(1, ctx->opt_blocks_per_sm), R.bound), threads, 0, gs>>>(V, Q, it);
         PTB_CUDA(ctx, mark(3));
         rs.launches += 2;
         if (V.enable_nee)
@@ -1203,14 +1395,15 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             if (bin) k_nee_bin<<<grid, threads, 0, gs>>>(V, Q, it);
             else
             {
-                const int ng = ctx->sm_count * ctx->opt_nee_blocks;
-                switch (ctx->opt_nee_blocks)
+                const int nb = (ctx->opt_nee_blocks == 4 || ctx->opt_nee_blocks == 6 || ctx->opt_nee_blocks == 7 || ctx->opt_nee_blocks == 8) ? ctx->opt_nee_blocks : 5;
+                const int ng = sized_grid(nb, R.bound);
+                switch (nb)
                 {
                 case 4: k_nee<4><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
                 case 7: k_nee<7><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
                 case 8: k_nee<8><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
                 case 6: k_nee<6><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
-                default: k_nee<5><<<ctx->sm_count * 5, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
+                default: k_nee<5><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
                 }
             }
             PTB_CUDA(ctx, mark(4));
@@ -1227,10 +1420,17 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             PTB_CUDA(ctx, cudaEventSynchronize(rs.poll_events[(size_t)g * NEV + (it - LAG) % NEV]));
             const uint32_t* f = &R.h_flags[((it - LAG) % POLL_RING) * 4];
             const uint32_t active = f[0] + f[1];
+            R.bound = active;
             if (active == 0u) { R.done = true; return PTB_OK; }
-            const bool to_tail = active <= tail_threshold;
+            const bool to_path = active <= path_threshold;
+            const bool to_tail = !to_path && active <= tail_threshold;
             // live slots scattered thinly over the listed groups: the queue shade kernel from the next iteration on (the queues are valid as they are)
             if (dense && (uint64_t)active * 100u < dense_pct * 32u * (uint64_t)f[3]) R.dense = false;
+            if (to_path)
+            {
+                const int rc = launch_path(g, it + 1u);
+                if (rc != PTB_OK) return rc;
+            }
             if (to_tail)
             {
                 // active counts never grow: `active` bounds the queue at it+1
@@ -1247,6 +1447,13 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         }
         return PTB_OK;
     };
+    // a group that starts at or below the path threshold never enters the wavefront loop: k_init's queues are k_path's input
+    for (int g = 0; g < G; ++g)
+        if (gr[g].Q.npix <= path_threshold)
+        {
+            const int rc = launch_path(g, 0u);
+            if (rc != PTB_OK) return rc;
+        }
     for (int running = G; running > 0;)
     {
         running = 0;
@@ -1290,6 +1497,25 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         if (launch_log) std::fclose(launch_log);
     }
     return PTB_OK;
+}
+
+// Frame-after-frame hosts (the reference's loop, main.rs:179-219): the wavefront of one frame thins out into ~10^2 latency-bound
+// iterations and a tail during which most of the device idles (C3: 30 % of the frame for 8 % of its rays).  A second context on
+// the same device fills that time with the dense phase of the next frame: ptb_render_async returns at once, the render loop runs
+// on a worker thread of the context, ptb_wait joins it.  Between the two calls the context must not be used otherwise.
+int ptb_render_async(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_bounces, int enable_nee)
+{
+    REQUIRE_DEVICE(ctx);
+    if (ctx->async_thread) return ctx->fail(PTB_ERR_INVALID, "ptb_render_async: a render is already in flight on this context (call ptb_wait)");
+    ctx->async_rc = PTB_OK;
+    ctx->async_thread = new (std::nothrow) std::thread([=] { ctx->async_rc = ptb_render(ctx, sample_begin, sample_count, seed, max_bounces, enable_nee); });
+    if (!ctx->async_thread) return ctx->fail(PTB_ERR_OOM, "ptb_render_async: no worker thread");
+    return PTB_OK;
+}
+int ptb_wait(ptb_context* ctx)
+{
+    if (!ctx) return PTB_ERR_INVALID;
+    return ctx->wait_async();  // the worker's status; its message is ptb_last_error
 }
 
 int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active, uint32_t* count)
@@ -1343,7 +1569,7 @@ int ptb_get_counters(ptb_context* ctx, uint64_t out[8])
     for (int g = 0; g < MAX_GROUPS; ++g)  // one counter block per wavefront group; iterations: the longest group
     {
         c.stat_extend += cg[g].stat_extend; c.stat_shadow += cg[g].stat_shadow; c.stat_probe += cg[g].stat_probe; c.stat_paths += cg[g].stat_paths;
-        c.stat_probe_shadow += cg[g].stat_probe_shadow; c.stat_iters = std::max(c.stat_iters, cg[g].stat_iters);
+        c.stat_probe_shadow += cg[g].stat_probe_shadow; c.stat_iters = std::max(c.stat_iters, cg[g].stat_iters); c.stat_settled += cg[g].stat_settled; c.stat_extend_path += cg[g].stat_extend_path;
     }
     out[0] = c.stat_extend;
     out[1] = c.stat_shadow + c.stat_probe_shadow;
@@ -1351,8 +1577,8 @@ int ptb_get_counters(ptb_context* ctx, uint64_t out[8])
     out[3] = c.stat_paths;
     out[4] = c.stat_iters;
     out[5] = ctx->rs->launches;
-    out[6] = c.stat_paths;  // every path starts with exactly one primary ray
-    out[7] = 0;
+    out[6] = c.stat_extend_path;  // part of [0] traced by the single-launch kernels (k_path, tail) rather than by k_extend launches
+    out[7] = c.stat_settled;  // primary rays of a camera outside the scene bounds that the bounds pre-test settled without a traversal (not in [0])
     return PTB_OK;
 }
 int ptb_reset_counters(ptb_context* ctx)

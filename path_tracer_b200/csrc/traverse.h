@@ -96,12 +96,26 @@ PTB_HD void transform_ray_reuse(TravRay& out, V3 o, V3 d, V3 inv_d, const float*
     out.oi = 7u ^ oct;
 }
 
-PTB_HD float qbyte_biased(uint32_t w, int k)
+// `kc` = 0x4B000000 read from constant memory (qbyte_const), which the compiler cannot see through: PRMT then takes the byte selector as its
+// immediate.  Given the literal, ptxas puts the LITERAL into the immediate slot and the selector into a register that the result
+// overwrites, i.e. one extra MOV per byte — 51 of the 292 instructions of the node stage (profiles/r2a_c3_extend_sass.txt).
+#if defined(__CUDACC__)
+static __constant__ uint32_t g_qbyte_kc = 0x4B000000u;  // read through the constant bank: ptxas cannot fold it back into a literal
+#endif
+PTB_HD uint32_t qbyte_const()
 {
 #if defined(__CUDA_ARCH__)
-    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7504u | ((uint32_t)k << 4)));
+    return g_qbyte_kc;
 #else
-    return ex::from_bits(0x4B000000u | (((w >> (8 * k)) & 0xffu) << 8));
+    return 0x4B000000u;
+#endif
+}
+PTB_HD float qbyte_biased(uint32_t w, int k, uint32_t kc)
+{
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(w, kc, 0x7504u | ((uint32_t)k << 4)));
+#else
+    return ex::from_bits(kc | (((w >> (8 * k)) & 0xffu) << 8));
 #endif
 }
 
@@ -141,14 +155,15 @@ PTB_HD uint32_t wide_node_test(const uint4& q0, const uint4& q2, const uint4& q3
     const uint32_t ny0 = ny ? hiy0 : loy0, ny1 = ny ? hiy1 : loy1, fy0 = ny ? loy0 : hiy0, fy1 = ny ? loy1 : hiy1;
     const uint32_t nz0 = nz ? hiz0 : loz0, nz1 = nz ? hiz1 : loz1, fz0 = nz ? loz0 : hiz0, fz1 = nz ? loz1 : hiz1;
     uint32_t mask = 0;
+    const uint32_t kc = qbyte_const();
 #pragma unroll
     for (int s = 0; s < 8; ++s)
     {
         const int b4 = s & 3;
         const uint32_t wnx = s < 4 ? nx0 : nx1, wfx = s < 4 ? fx0 : fx1, wny = s < 4 ? ny0 : ny1, wfy = s < 4 ? fy0 : fy1, wnz = s < 4 ? nz0 : nz1, wfz = s < 4 ? fz0 : fz1;
-        const float tnx = fmaf(qbyte_biased(wnx, b4), s8x, cnx), tfx = fmaf(qbyte_biased(wfx, b4), s8x, cfx);
-        const float tny = fmaf(qbyte_biased(wny, b4), s8y, cny), tfy = fmaf(qbyte_biased(wfy, b4), s8y, cfy);
-        const float tnz = fmaf(qbyte_biased(wnz, b4), s8z, cnz), tfz = fmaf(qbyte_biased(wfz, b4), s8z, cfz);
+        const float tnx = fmaf(qbyte_biased(wnx, b4, kc), s8x, cnx), tfx = fmaf(qbyte_biased(wfx, b4, kc), s8x, cfx);
+        const float tny = fmaf(qbyte_biased(wny, b4, kc), s8y, cny), tfy = fmaf(qbyte_biased(wfy, b4, kc), s8y, cfy);
+        const float tnz = fmaf(qbyte_biased(wnz, b4, kc), s8z, cnz), tfz = fmaf(qbyte_biased(wfz, b4, kc), s8z, cfz);
         const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, ex::EPS));
         const float tf = fminf(fminf(tfx, tfy), fminf(tfz, t_max));
         if (tn <= tf) mask |= (1u << s);

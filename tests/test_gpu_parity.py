@@ -120,6 +120,7 @@ def test_render_same_streams(ptb, po, scenes, name, nee, kernel):
     pos, ids = ctx.read_aux()
     ref = sc.render(width=W, height=H, sample_count=N, seed=5, enable_nee=nee)
     cnt = ctx.counters()
+    cnt["extend"] += cnt["settled"]  # primaries settled by the bounds pre-test are the reference's root-box misses (tlas.rs:68): rays of the oracle's count
     for k in ("extend", "shadow", "probe", "paths"):
         assert abs(cnt[k] - ref["counters"][k]) <= 0.01 * ref["counters"][k] + 2, (k, cnt[k], ref["counters"][k])  # libm ulps can fork a few glossy paths
     assert np.all(img[..., 3] == N)
@@ -288,7 +289,7 @@ def test_slot_ordered_and_queue_kernels_agree(ptb, scenes, name, spp, W, H):
         ctx.render(0, spp, seed=11, max_bounces=sd.max_bounces)
         pos, ids = ctx.read_aux()
         c = ctx.counters()
-        out[(dense, thr)] = (ctx.read_accum(), bits(pos), ids, (c["extend"], c["shadow"], c["probe"], c["paths"]))
+        out[(dense, thr)] = (ctx.read_accum(), bits(pos), ids, (c["extend"] + c["settled"], c["shadow"], c["probe"], c["paths"]))
     ref = out[(0, 0)]
     for k, v in out.items():
         assert np.array_equal(ref[1], v[1]) and np.array_equal(ref[2], v[2]), f"dense={k}: first-hit position / id differ from the queue kernels"
@@ -320,3 +321,98 @@ def test_wavefront_groups_and_tail_layout_do_not_change_results(ptb, scenes, nam
     for G, v in out.items():
         assert all(np.array_equal(a, b) for a, b in zip(out[1][:3], v[:3])), f"wavefront_groups={G}: outputs differ"
         assert out[1][3] == v[3], f"wavefront_groups={G}: ray counters differ"
+
+
+@pytest.mark.parametrize("name,spp,W,H", [("c2", 6, 96, 54), ("c3_small", 5, 97, 53), ("materials", 19, 33, 21), ("c1", 4, 64, 36)])
+def test_path_kernel_equals_wavefront(ptb, scenes, name, spp, W, H):
+    """k_path (every remaining slot run to completion in one persistent launch: extend -> shade -> NEE rays -> next bounce ->
+    regeneration chained per lane) against the three-kernel wavefront + tail kernels it replaces, switch-over at every point:
+    never (path_threshold = 0), from the first iteration on (the whole render in k_path), and in between.  Same per-slot bodies on
+    the same per-slot RNG streams: first-hit position, ids and ray counts identical, radiance equal to rounding (the compiler
+    contracts the shading arithmetic per kernel)."""
+    sd = _scene(scenes, name)
+    out = {}
+    for thr, fq, blocks in ((0, 8, 5), (1 << 30, 8, 5), (1 << 30, 1, 4), (1 << 30, 32, 6), (W * H * 2, 8, 5), (500, 4, 5)):
+        ctx = ptb.Context(0)
+        ctx.upload(sd)
+        ctx.set_option("path_threshold", thr)
+        ctx.set_option("finish_quorum", fq)
+        ctx.set_option("path_blocks", blocks)
+        ctx.set_option("wavefront_groups", 1 if thr != 500 else 2)
+        ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
+        ctx.frame_begin(W, H)
+        ctx.reset_counters()
+        ctx.render(0, spp, seed=17, max_bounces=sd.max_bounces)
+        pos, ids = ctx.read_aux()
+        c = ctx.counters()
+        out[(thr, fq, blocks)] = (ctx.read_accum(), bits(pos), ids, (c["extend"] + c["settled"], c["shadow"], c["probe"], c["paths"]), c)
+    ref = out[(0, 8, 5)]
+    assert ref[4]["extend_path"] < ref[4]["extend"]
+    whole = out[(1 << 30, 8, 5)][4]
+    assert whole["extend_path"] == whole["extend"] and whole["iterations"] == 0, "path_threshold above the slot count: the whole render runs in k_path"
+    for k, v in out.items():
+        assert np.array_equal(ref[1], v[1]) and np.array_equal(ref[2], v[2]), f"{k}: first-hit position / id differ from the wavefront kernels"
+        assert ref[3] == v[3], f"ray counters differ for {k}: {ref[3]} vs {v[3]}"
+        assert np.array_equal(ref[0][..., 3], v[0][..., 3])
+        assert np.allclose(ref[0], v[0], rtol=1e-5, atol=1e-7), f"{k}: radiance differs beyond rounding"
+
+
+def _group_render(group, sd, W, H, begin, count, seed):
+    group.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
+    group.frame_begin(W, H)
+    group.reset_counters()
+    group.render(begin, count, seed=seed, max_bounces=sd.max_bounces)
+    group.reduce(0)
+    return group.read_accum(0), group.read_aux(0), group.counters()
+
+
+def test_group_api_single_device(ptb, scenes):
+    """ptb_group_* (csrc/group.cu) on a group of one device: partition arithmetic, broadcast helpers, the NCCL reduce (one rank:
+    in place) and the reads must reproduce ptb_render on a plain context bit for bit."""
+    from path_tracer_b200 import multi
+    sd = scenes.scene_c2()
+    W, H, begin, count, seed = 96, 54, 3, 7, 23
+    g = multi.Group.create([0])
+    assert (g.n_local, g.n_ranks) == (1, 1)
+    g.upload(sd)
+    acc, (pos, ids), c = _group_render(g, sd, W, H, begin, count, seed)
+    ctx = ptb.Context(0)
+    ctx.upload(sd)
+    ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
+    ctx.frame_begin(W, H)
+    ctx.reset_counters()
+    ctx.render(begin, count, seed=seed, max_bounces=sd.max_bounces)
+    assert np.array_equal(bits(acc), bits(ctx.read_accum()))
+    p2, i2 = ctx.read_aux()
+    assert np.array_equal(bits(pos), bits(p2)) and np.array_equal(ids, i2)
+    c2 = ctx.counters()
+    assert all(c[k] == c2[k] for k in ("extend", "shadow", "probe", "paths", "settled"))
+    assert g.reduce_ms() >= 0.0
+    for begin_, count_, world in ((0, 64, 8), (5, 7, 4), (0, 3, 8), (100, 4096, 3)):
+        for r in range(world):
+            assert multi.lib_sample_range(begin_, count_, r, world) == multi.sample_range(begin_, count_, r, world)
+    g.close()
+
+
+def test_group_two_devices_equals_one(ptb, scenes):
+    """SURVEY Appendix C, multi-GPU row: the image a 2-GPU group reduces with NCCL equals the 1-GPU image of the same global sample
+    range — same sample set, so only the float summation order differs (<= 1e-6 relative on the sums), w identical, ray counters
+    identical; aux outputs are the root's own last sample."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    from path_tracer_b200 import multi
+    sd = scenes.scene_c3(grid=8)
+    W, H, begin, count, seed = 160, 90, 2, 9, 29
+    g2 = multi.Group.create([0, 1])
+    g2.upload(sd)
+    acc2, _, c2 = _group_render(g2, sd, W, H, begin, count, seed)
+    g2.close()
+    g1 = multi.Group.create([0])
+    g1.upload(sd)
+    acc1, _, c1 = _group_render(g1, sd, W, H, begin, count, seed)
+    g1.close()
+    assert np.array_equal(acc1[..., 3], acc2[..., 3]) and np.all(acc1[..., 3] == count)
+    assert all(c1[k] == c2[k] for k in ("extend", "shadow", "probe", "paths", "settled")), (c1, c2)
+    err = np.abs(acc1[..., :3] - acc2[..., :3]).max(axis=2)
+    assert np.all(err <= 1e-6 * np.abs(acc1[..., :3]).max(axis=2) + 1e-9), f"max abs diff {err.max()}"
