@@ -215,6 +215,9 @@ int ptb_set_profiling(ptb_context* ctx, int enable);
 int ptb_get_timing(ptb_context* ctx, float times_ms[8], uint32_t launches[8]);
 /* Active slots (paths in flight + slots awaiting regeneration) after each wavefront iteration of the last ptb_render (first 8192). */
 int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active, uint32_t* count);
+/* Every kernel launch of the last ptb_render that ran with profiling on, in launch order: stage index as in ptb_get_timing
+ * (2 extend, 3 shade, 4 nee, 5 tail / path, 6 combine) and its duration in microseconds (CUDA events on the context stream). */
+int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, float* microseconds, uint32_t* count);
 /* Tunables (evidence switches for DESIGN.md's layout decisions), name = value:
  *   extend_kernel     0 the 8-wide persistent kernels (default), 1 the reference-order kernels over the reference's binary trees
  *   wide_collapse     8-wide collapse of the reference trees at the next ptb_build: 1 least summed node area (default), 0 greedy
@@ -236,6 +239,18 @@ int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active,
  *   block_threads, blocks_per_sm     launch shape of the queue shade / reference-order kernels */
 int ptb_set_option(ptb_context* ctx, const char* name, int value);
 
+
+/* ---- load_obj  blas.rs:44-131 ---------------------------------------------------------------------------------------------
+ * The reference's only on-disk input: an OBJ file -> the triangle vertex array ptb_scene_upload takes (ntri * 3 vertices x
+ * (position xyz, normal xyz)), with load_obj's rules: `v` / `vn` / `f` lines only, 1-based indices (negative = from the end), `vn`
+ * normalised on load, every face token v/vt/vn or v//vn, fan triangulation (refs[0], refs[i], refs[i+1]; a face of one or two
+ * references yields nothing, blas.rs:97), normal index 0 -> the un-normalised face normal cross(p1-p0, p2-p0) (blas.rs:109-116).
+ * Where the reference panics (bad number, index out of bounds, empty line) these return PTB_ERR_INVALID; ptb_load_obj_error gives
+ * the message with the line number.  *verts is allocated by the library: release it with ptb_free.  Host code, no device needed. */
+int ptb_load_obj(const char* path, float** verts, uint64_t* ntri);
+int ptb_load_obj_text(const char* text, size_t len, float** verts, uint64_t* ntri);
+const char* ptb_load_obj_error(void);
+void ptb_free(void* p);
 
 /* ---- multi-GPU: sample-partitioned rendering, one NCCL reduce per frame batch ---------------------------------
  * The frame loop main.rs:181-207 is a pure map over (pixel, sample) and the accumulation (accumulate.wgsl:23) a commutative

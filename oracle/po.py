@@ -30,7 +30,7 @@ class Instance(C.Structure):
 
 def build(force=False):
     so = os.path.join(_HERE, "libpt_oracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("po_capi.cpp", "po_math.hpp", "po_accel.hpp", "po_shading.hpp", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("po_capi.cpp", "po_math.hpp", "po_accel.hpp", "po_shading.hpp", "po_temporal.hpp", "po_obj.hpp", "Makefile")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return so
@@ -224,6 +224,19 @@ class OracleScene:
                                int(enable_nee), threads, _p(accum), _p(sq), _p(pos), _p(ids), _p(cnt))
         names = ["extend", "shadow", "probe", "paths", "bounces", "extend_boxes", "extend_tris", "extend_insts", "light_boxes", "light_tris", "light_insts", "shadow_boxes", "shadow_tris", "shadow_insts"]
         return dict(accum=accum, accum_sq=sq, position=pos, id=ids, seconds=secs, counters={k: int(v) for k, v in zip(names, cnt)})
+
+
+def load_obj_text(text):
+    """load_obj (blas.rs:44-131) on a text image -> float32 [ntri, 3, 6]; ValueError where the reference panics."""
+    b = text.encode() if isinstance(text, str) else bytes(text)
+    n = C.c_uint64()
+    L = lib()
+    if L.po_load_obj_text(b, C.c_uint64(len(b)), None, C.byref(n)):
+        raise ValueError(L.po_last_error().decode())
+    out = np.zeros((n.value, 3, 6), np.float32)
+    if n.value:
+        L.po_load_obj_text(b, C.c_uint64(len(b)), _p(out), C.byref(n))
+    return out
 
 
 def generate_blas_span(boxes, prims, last_axis=4):

@@ -8,6 +8,7 @@
 #include <string>
 #include <thread>
 
+#include "po_obj.hpp"
 #include "po_shading.hpp"
 #include "po_temporal.hpp"
 
@@ -531,6 +532,29 @@ double po_render(const po_scene* s, const float* cam_origin, const float* cam_ta
             counters[11] += rc.shadow_w.boxes; counters[12] += rc.shadow_w.tris; counters[13] += rc.shadow_w.insts;
         }
     return el;
+}
+
+// load_obj (blas.rs:44-131) on a text image.  Two calls: with out == nullptr it only counts; otherwise it fills ntri*18 floats.
+// Returns 0, or 1 where the reference would panic (message in po_last_error).
+int po_load_obj_text(const char* text, uint64_t len, float* out, uint64_t* ntri)
+{
+    try
+    {
+        const std::vector<ObjVertex> v = load_obj_text(std::string(text, (size_t)len));
+        *ntri = v.size() / 3;
+        if (out)
+            for (size_t i = 0; i < v.size(); ++i)
+            {
+                out[i * 6 + 0] = v[i].position.x; out[i * 6 + 1] = v[i].position.y; out[i * 6 + 2] = v[i].position.z;
+                out[i * 6 + 3] = v[i].normal.x; out[i * 6 + 4] = v[i].normal.y; out[i * 6 + 5] = v[i].normal.z;
+            }
+        return 0;
+    }
+    catch (ObjError& e)
+    {
+        g_err = e.msg;
+        return 1;
+    }
 }
 
 }  // extern "C"

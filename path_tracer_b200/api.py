@@ -27,13 +27,13 @@ EXPORTS = [
     "ptb_light_count", "ptb_light_sampler", "ptb_bvh_stats", "ptb_trace_closest", "ptb_trace_any", "ptb_trace_upload", "ptb_trace_resident",
     "ptb_trace_download", "ptb_set_camera", "ptb_camera_rays", "ptb_ss_sobol", "ptb_rng_stream", "ptb_frame_begin", "ptb_render", "ptb_render_async", "ptb_wait", "ptb_read_accum",
     "ptb_read_aux", "ptb_read_rgb8", "ptb_enable_second_moment", "ptb_read_second_moment", "ptb_accum_device_ptr", "ptb_bind_accum", "ptb_get_counters",
-    "ptb_reset_counters", "ptb_set_profiling", "ptb_get_timing", "ptb_get_iteration_log", "ptb_set_option",
+    "ptb_reset_counters", "ptb_set_profiling", "ptb_get_timing", "ptb_get_iteration_log", "ptb_get_launch_log", "ptb_set_option",
     "ptb_state_reset", "ptb_state_update", "ptb_state_update_resident", "ptb_state_read", "ptb_state_read_rgb8", "ptb_state_device_ptr", "ptb_state_timing", "ptb_frame_next",
     "ptb_camera_view_projection",
     "ptb_group_create", "ptb_group_unique_id", "ptb_group_join", "ptb_group_destroy", "ptb_group_last_error", "ptb_group_size", "ptb_group_context",
     "ptb_group_sample_range", "ptb_group_scene_upload", "ptb_group_build", "ptb_group_set_camera", "ptb_group_set_option", "ptb_group_frame_begin",
     "ptb_group_render", "ptb_group_reduce", "ptb_group_read_accum", "ptb_group_read_aux", "ptb_group_get_counters", "ptb_group_reset_counters",
-    "ptb_group_reduce_ms",
+    "ptb_group_reduce_ms", "ptb_load_obj", "ptb_load_obj_text", "ptb_load_obj_error", "ptb_free",
 ]
 # ptb_get_counters: [0] extend rays that ran a traversal, [7] primary rays settled by the bounds pre-test without one (k_extend)
 COUNTER_NAMES = ["extend", "shadow", "probe", "paths", "iterations", "launches", "extend_path", "settled"]
@@ -409,6 +409,14 @@ class Context:
         n = C.c_uint32()
         self._ck(self.L.ptb_get_iteration_log(self.h, capacity, _p(a), C.byref(n)))
         return a[: n.value]
+
+    def launch_log(self, capacity=1 << 16):
+        """(stage, microseconds) arrays of every launch of the last render that ran with profiling on."""
+        st = np.zeros(capacity, np.int32)
+        us = np.zeros(capacity, np.float32)
+        n = C.c_uint32()
+        self._ck(self.L.ptb_get_launch_log(self.h, capacity, _p(st), _p(us), C.byref(n)))
+        return st[: n.value], us[: n.value]
 
     def set_option(self, name, value):
         self._ck(self.L.ptb_set_option(self.h, name.encode(), int(value)))

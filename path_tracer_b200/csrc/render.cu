@@ -85,6 +85,7 @@ struct RenderState
     float t_class_ms[8] = {0};
     uint32_t n_class[8] = {0};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    std::vector<std::pair<int, float>> launch_log;  // (stage class, microseconds) of every launch of the last profiled ptb_render
     int tail_capacity = -1;  // slots the tail kernel (tail_kind: 1 = k_tail_roles, 0 = k_tail) keeps resident on this device
     int tail_kind = -1;
 };
@@ -1448,11 +1449,18 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         return PTB_OK;
     };
     // a group that starts at or below the path threshold never enters the wavefront loop: k_init's queues are k_path's input
+    // error exit from the launch loop: kernels of the forked group streams may still be running — drain them before handing the
+    // context back, or a later call on ctx->stream would race with them
+    auto abandon = [&](int rc) -> int {
+        for (int g = 1; g < G; ++g) cudaStreamSynchronize(gr[g].st);
+        cudaStreamSynchronize(st);
+        return rc;
+    };
     for (int g = 0; g < G; ++g)
         if (gr[g].Q.npix <= path_threshold)
         {
             const int rc = launch_path(g, 0u);
-            if (rc != PTB_OK) return rc;
+            if (rc != PTB_OK) return abandon(rc);
         }
     for (int running = G; running > 0;)
     {
@@ -1461,7 +1469,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         {
             if (gr[g].done) continue;
             const int rc = step_group(g);
-            if (rc != PTB_OK) return rc;
+            if (rc != PTB_OK) return abandon(rc);
             if (!gr[g].done) ++running;
         }
     }
@@ -1486,12 +1494,14 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         // development aid: PTB_LAUNCH_LOG=<file> lists every launch of the render (stage class, microseconds)
         const char* log_path = std::getenv("PTB_LAUNCH_LOG");
         std::FILE* launch_log = log_path ? std::fopen(log_path, "w") : nullptr;
+        rs.launch_log.clear();
         for (size_t i = 1; i < prof_used; ++i)
         {
             float d = 0;
             PTB_CUDA(ctx, cudaEventElapsedTime(&d, rs.prof_events[i - 1], rs.prof_events[i]));
             const int cls = prof_class[i];
             if (cls >= 1 && cls < 8) { rs.t_class_ms[cls] += d; rs.n_class[cls] += 1; }
+            rs.launch_log.emplace_back(cls, d * 1000.0f);
             if (launch_log) std::fprintf(launch_log, "%d %.3f\n", cls, d * 1000.0f);
         }
         if (launch_log) std::fclose(launch_log);
@@ -1516,6 +1526,20 @@ int ptb_wait(ptb_context* ctx)
 {
     if (!ctx) return PTB_ERR_INVALID;
     return ctx->wait_async();  // the worker's status; its message is ptb_last_error
+}
+
+int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, float* microseconds, uint32_t* count)
+{
+    REQUIRE_DEVICE(ctx);
+    if (!ctx->rs || !count) return ctx->fail(PTB_ERR_INVALID, "no frame");
+    const uint32_t n = std::min<uint32_t>((uint32_t)ctx->rs->launch_log.size(), capacity);
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        if (stage) stage[i] = ctx->rs->launch_log[i].first;
+        if (microseconds) microseconds[i] = ctx->rs->launch_log[i].second;
+    }
+    *count = n;
+    return PTB_OK;
 }
 
 int ptb_get_iteration_log(ptb_context* ctx, uint32_t capacity, uint32_t* active, uint32_t* count)

@@ -170,6 +170,9 @@ int ptb_state_update(ptb_context* ctx, uint32_t width, uint32_t height, const fl
     PTB_CUDA(ctx, cudaMemcpyAsync(ts.in_data.p, data, npix * 16, cudaMemcpyHostToDevice, ctx->stream));
     PTB_CUDA(ctx, cudaMemcpyAsync(ts.in_position.p, position, npix * 16, cudaMemcpyHostToDevice, ctx->stream));
     PTB_CUDA(ctx, cudaMemcpyAsync(ts.in_id.p, id, npix * 4, cudaMemcpyHostToDevice, ctx->stream));
+    // the host arrays are borrowed for the duration of the call only (ptb.h): with pinned memory the copies above are truly
+    // asynchronous, and the reference's caller overwrites these arrays for the next frame (main.rs:204-206) — wait for them here
+    PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return temporal_update_device(ctx, ts.in_data.p, ts.in_position.p, ts.in_id.p, inv_projection, last_inv_projection, 0);
 }
 

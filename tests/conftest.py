@@ -32,7 +32,15 @@ def same_bits_or_nan(a, b):
     return a.shape == b.shape and bool(np.all((bits(a) == bits(b)) | (np.isnan(a) & np.isnan(b))))
 
 
+# SURVEY H2 expects ties within 1 ulp.  Measured (tests print the histogram, TIE_LOG collects it): most are, but on terrain-like meshes
+# (c4) a few per 10^5 rays sit 2-4 ulps apart — two triangles sharing an edge, hit almost on that edge: the reference keeps whichever
+# it tests LAST among candidates that pass `t in [t_min, t_max]` evaluated in the frame translated by the leaf's t_enter
+# (primitive.rs:147-155), where t_max - t_estimate is rounded to the grid of the (larger) t_estimate; a candidate up to a few ulps
+# NEARER than the current hit can fail that test, one a few ulps FARTHER can pass it.  Which of the two survives depends on visit
+# order, so only the reference-order kernel reproduces it; for the 8-wide kernel such pairs are ties up to TIE_ULPS = 4 (<= 5e-7
+# relative, the north star allows 1e-5 on t).  DESIGN.md section 2 lists examples.
 TIE_ULPS = 4
+TIE_LOG = []  # (ulps between the two candidates' t) of every classified tie of this session
 
 
 def compare_closest(ref, got, oracle_scene, o, d, tmax, which=0, allow_ties=True):
@@ -62,6 +70,7 @@ def compare_closest(ref, got, oracle_scene, o, d, tmax, which=0, allow_ties=True
         ok_g, t_g = oracle_scene.eval_candidate(got["inst"][i], got["prim"][i], o[i], d[i], tmax[i], which=which)
         assert ok_r and ok_g, f"ray {i}: a reported winner is not a hit"
         assert ulp_diff(np.float32(t_r), np.float32(t_g)) <= TIE_ULPS, f"ray {i}: not a tie: {t_r} vs {t_g}"
+        TIE_LOG.append(int(ulp_diff(np.float32(t_r), np.float32(t_g))))
         assert ulp_diff(ref["t"][i], got["t"][i]) <= TIE_ULPS
     return int(same.sum()), int(len(idx))
 

@@ -143,3 +143,33 @@ def test_large_build_properties_and_subtrees(po, scenes):
             assert np.array_equal(r["leaf_prims"][a1:a1 + c1], lp[a2:a2 + c2])
         checked += 1
     assert checked == 6
+
+
+def test_full_size_c3_build(po, scenes):
+    """BASELINE config 2 at its stated size: 1026 instances (two 1024-triangle tori BLASes, ground, emitter), 1 048 580 instanced
+    triangles — every Appendix-A array of the product build against the oracle's, bit for bit (the agglomerative TLAS over 1026
+    leaves included, tlas_bvh.rs:106-135)."""
+    sd = scenes.scene_c3()
+    assert sd.instanced_tris == 1048580 and len(sd.instances) == 1026
+    _check_scene(po, sd)
+
+
+def test_full_size_c4_build_golden_hash(scenes):
+    """BASELINE config 3 at its stated size (9 999 392-triangle terrain + 128 icospheres + emitter): the product build (scan-based,
+    sub-tree parallel) against golden sha256 hashes of the Appendix-A arrays that the oracle's literal restatement produced once
+    (tests/golden/make_golden_c4.py; the oracle needs ~40 s for this tree, so it is not rebuilt here)."""
+    import json
+    import os
+    import sys
+    import path_tracer_b200 as ptb
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, os.path.join(here, "golden"))
+    from make_golden_c4 import build_hashes
+    gold = json.load(open(os.path.join(here, "golden", "build_c4_full_hashes.json")))
+    sd = scenes.scene_c4()
+    assert sd.verts.shape[0] == gold["triangles"] == 10001954
+    ctx = ptb.Context(-1)
+    ctx.upload(sd)
+    got = build_hashes(ctx, len(sd.blas))
+    for k, v in gold["arrays"].items():
+        assert got[k] == v, f"{k}: product build differs from the oracle's golden hashes"

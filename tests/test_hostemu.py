@@ -57,7 +57,7 @@ def test_camera_rays(po, scenes, emu):
     st = scenes.pixel_centre_st(320, 180)
     o1, d1 = po.camera_rays(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(320 / 180), st)
     o2, d2 = emu.camera_rays(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(320 / 180), st)
-    assert np.array_equal(o1, o2) and np.abs(d1 - d2).max() <= 2e-7  # tolerance tier; observed bit-equal
+    assert np.array_equal(bits(o1), bits(o2)) and np.array_equal(bits(d1), bits(d2))  # camera.rs is in the bit-exact tier
 
 
 @pytest.mark.parametrize("name,nee", [("c2", True), ("c2", False), ("c1", True), ("materials", True)])
