@@ -123,7 +123,8 @@ int ptb_bvh_stats(ptb_context* ctx, uint64_t out[8]);
 
 /* ---- fixed ray batches: TLAS::intersect (tlas.rs:66-110) / TLAS::any_intersect (tlas.rs:111-144) ---------------
  * which: 0 = scene.world, 1 = scene.lights.  kernel: 0 = 8-wide persistent kernel (the renderer's), 1 = reference-order
- * binary kernel (walks the reference's own binary BVH in the reference's visit order; bit-exact incl. ties).
+ * binary kernel (walks the reference's own binary BVH in the reference's visit order; bit-exact incl. ties), 2 = team kernel
+ * (eight lanes per ray over the 8-wide layout, csrc/team.cuh; same results as kernel 0 up to the resolution of exact ties).
  * o3/d3: n*3 floats (d normalised, ray.rs:12), tmax: n floats.  Host pointers; copies happen inside the call.
  * Outputs may be NULL except `hit`.  blas = scene blas index, inst = instance ordinal (`Model`x`matrices` order),
  * normal = world-space ray-facing shading normal (primitive.rs:161-165, tlas.rs:103-105). */
@@ -236,6 +237,15 @@ int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, floa
  *   tail_slots_per_block   slots per three-warp block of that kernel, 1..32 (default 32; same results)
  *   wavefront_groups  independent wavefronts per render, each over 1/G of the slots with its own queues on its own stream,
  *                     1..8 (default 2; bit-identical results for every G; forced to 1 while profiling is on)
+ *   path_threshold    active slots at which ALL remaining slots go to the persistent path kernel k_path (extend -> shade -> NEE
+ *                     rays -> next bounce chained per lane in one launch); 0 = never (default: measured slower than thin wavefront
+ *                     iterations + tail kernel), < 0 automatic; path_blocks (4..6) and finish_quorum (1..32,
+ *                     lanes with a finished traversal that make a warp leave the stepping loop and shade) tune it (same results)
+ *   stack_shared      first 8 / 12 / 16 entries of every thread's traversal stack in shared memory instead of local memory
+ *                     (k_extend<7> / k_nee<8>; 0 = local memory only, the default — measured; same results)
+ *   shared_device     1: another context renders on this device at the same time (ptb_render_async pairs): persistent grids leave
+ *                     one block slot per SM free;  thin_rays_per_lane > 0: persistent kernels take only the blocks their queue
+ *                     fills at that many entries per lane (both 0 by default; same results)
  *   block_threads, blocks_per_sm     launch shape of the queue shade / reference-order kernels */
 int ptb_set_option(ptb_context* ctx, const char* name, int value);
 

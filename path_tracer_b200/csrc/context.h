@@ -98,6 +98,7 @@ struct ptb_context
     int opt_path_blocks = 5;      // resident blocks per SM (register cap) of k_path (4..6)
     int opt_shared_device = 0;    // 1: another context renders on this device at the same time (ptb_render_async pairs): leave it room, see sized_grid in render.cu
     int opt_thin_rays_per_lane = 0;  // > 0: persistent kernels take only ceil(live / (128 * this)) blocks once that is fewer than their full grid
+    int opt_stack_shared = 0;     // first N entries (0, 8, 12, 16) of each thread's traversal stack in shared memory (k_extend<7> / k_nee<8>), the rest in local memory
     int opt_finish_quorum = 8;    // k_path: lanes with a finished traversal that make the warp leave the stepping loop and shade
     int profiling = 0;
     int second_moment = 0;

@@ -4,6 +4,7 @@
 // layout (kernel = 1, the checker for traversal order): one ray per thread, grid-stride.  The per-ray work is traverse.h.
 #include "context.h"
 #include "persist.cuh"
+#include "team.cuh"
 
 namespace ptb {
 
@@ -85,6 +86,65 @@ __global__ void __launch_bounds__(128) trace_bin_kernel(SceneDev S, int which, u
     }
 }
 
+// team kernel (kernel = 2): eight lanes per ray, four rays per warp (team.cuh); a warp draws rays from a global cursor and deals them
+// to its teams as they finish, like persist.cuh does per lane
+template <bool ANY>
+__global__ void __launch_bounds__(128) trace_team_kernel(SceneDev S, int which, unsigned long long base, uint32_t n, TraceArgs a)
+{
+    __shared__ uint2 s_stack[TEAMS_PER_BLOCK][WIDE_STACK_CAP];
+    const unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u, tl = lane & 7u, tbase = lane & 24u, tmask = 0xffu << tbase;
+    uint2* stack = s_stack[threadIdx.x >> 3];
+    uint32_t* cursor = (uint32_t*)a.counter;
+    TeamRay tr;
+    unsigned long long i = 0;
+    bool active = false;
+    uint32_t wbase = 0, wend = 0;
+    bool more = n > 0u;
+    for (;;)
+    {
+        // deal rays to the idle teams of the warp
+        const unsigned idle = __ballot_sync(FULL, !active) & 0x01010101u;  // one bit per team (its lane 0)
+        if (idle && (wbase < wend || more))
+        {
+            if (wbase >= wend)
+            {
+                // 16 rays per atomic while the batch is much larger than the grid, else just what the idle teams need now: a warp must
+                // not sit on a private backlog while other warps have run dry (small batches are latency tests)
+                const uint32_t want = n > (gridDim.x * blockDim.x >> 5) * 64u ? 16u : (uint32_t)__popc(idle);
+                uint32_t b = 0;
+                if (lane == 0u) b = atomicAdd(cursor, want);
+                b = __shfl_sync(FULL, b, 0);
+                if (b >= n) more = false;
+                else { wbase = b; wend = min(b + want, n); if (wend == n) more = false; }
+            }
+            const uint32_t avail = wend - wbase, rank = (uint32_t)__popc(idle & ((1u << tbase) - 1u));
+            if (!active && rank < avail)
+            {
+                i = base + wbase + rank;
+                team_begin(tr, S, which, ex::v3(a.o[i * 3], a.o[i * 3 + 1], a.o[i * 3 + 2]), ex::v3(a.d[i * 3], a.d[i * 3 + 1], a.d[i * 3 + 2]), a.tmax[i]);
+                active = true;
+            }
+            wbase += min((uint32_t)__popc(idle), avail);
+        }
+        if (!__any_sync(FULL, active))
+        {
+            if (wbase >= wend && !more) break;
+            continue;
+        }
+        if (active && !team_step<ANY>(tr, S, stack, tl, tmask, tbase))
+        {
+            if (tl == 0u)
+            {
+                Hit h;
+                h.t = tr.t_max; h.u = ex::div(tr.hit_ud, tr.hit_det); h.v = ex::div(tr.hit_vd, tr.hit_det); h.slot_or_prim = tr.hit_slot; h.inst = tr.hit_inst;
+                write_result(S, which, a, i, ANY, tr.hit_inst != TRAV_NONE, h, 1u, tr.dw);
+            }
+            active = false;
+        }
+    }
+}
+
 cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream, int refill_below, int node_quorum)
 {
     const int blocks = sm_count * 8;
@@ -98,6 +158,17 @@ cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, 
             const uint32_t cnt = (uint32_t)std::min<uint64_t>(n - base, 0x40000000ull);
             if (any_hit) trace_wide_kernel<true><<<blocks, 128, 0, stream>>>(S, which, base, cnt, a, refill_below, node_quorum);
             else trace_wide_kernel<false><<<blocks, 128, 0, stream>>>(S, which, base, cnt, a, refill_below, node_quorum);
+        }
+    }
+    else if (kernel == 2)
+    {
+        for (uint64_t base = 0; base < n; base += 0x40000000ull)
+        {
+            cudaError_t e = cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), stream);
+            if (e != cudaSuccess) return e;
+            const uint32_t cnt = (uint32_t)std::min<uint64_t>(n - base, 0x40000000ull);
+            if (any_hit) trace_team_kernel<true><<<blocks, 128, 0, stream>>>(S, which, base, cnt, a);
+            else trace_team_kernel<false><<<blocks, 128, 0, stream>>>(S, which, base, cnt, a);
         }
     }
     else

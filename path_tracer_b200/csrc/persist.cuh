@@ -18,10 +18,17 @@
 
 namespace ptb {
 
-template <int MODE, class Job, bool GATED = false>
+template <int MODE, class Job, bool GATED = false, int SSTACK = 0>
 __device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, uint32_t* cursor, uint32_t total, int refill_below, int node_quorum, int finish_quorum = 33)
 {
-    uint2 stack[WIDE_STACK_CAP];
+    // traversal stack: local memory, or (SSTACK > 0, blocks of 128 threads) its first SSTACK entries in shared memory
+    uint2 lstack[WIDE_STACK_CAP - SSTACK];
+    __shared__ uint2 s_stack[SSTACK > 0 ? SSTACK : 1][SSTACK > 0 ? 128 : 1];
+    HybridStack<SSTACK, 128> hstack{&s_stack[0][SSTACK > 0 ? threadIdx.x : 0], lstack};
+    auto stack = [&]() {
+        if constexpr (SSTACK > 0) return hstack;
+        else return (uint2*)lstack;
+    }();
     WideTrav tr;
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;

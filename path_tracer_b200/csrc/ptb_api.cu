@@ -347,7 +347,7 @@ int ptb_trace_resident(ptb_context* ctx, int which, int kernel, int any_hit, int
     REQUIRE_DEVICE(ctx);
     REQUIRE_BUILT(ctx);
     if (ctx->t_n == 0) return ctx->fail(PTB_ERR_INVALID, "no resident ray batch: call ptb_trace_upload");
-    if (which < 0 || which > 1 || kernel < 0 || kernel > 1 || repeats < 1) return ctx->fail(PTB_ERR_INVALID, "bad arguments");
+    if (which < 0 || which > 1 || kernel < 0 || kernel > 2 || repeats < 1) return ctx->fail(PTB_ERR_INVALID, "bad arguments");
     PTB_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaEvent_t e0, e1;
     PTB_CUDA(ctx, cudaEventCreate(&e0));
@@ -385,7 +385,7 @@ int ptb_trace_closest(ptb_context* ctx, int which, int kernel, uint64_t n, const
     REQUIRE_DEVICE(ctx);
     REQUIRE_BUILT(ctx);
     if (!hit) return ctx->fail(PTB_ERR_INVALID, "hit output is required");
-    if (which < 0 || which > 1 || kernel < 0 || kernel > 1) return ctx->fail(PTB_ERR_INVALID, "bad which/kernel");
+    if (which < 0 || which > 1 || kernel < 0 || kernel > 2) return ctx->fail(PTB_ERR_INVALID, "bad which/kernel");
     if (n == 0) return PTB_OK;  // empty batch
     int rc = ptb_trace_upload(ctx, n, o3, d3, tmax);
     if (rc != PTB_OK) return rc;
@@ -411,7 +411,7 @@ int ptb_trace_any(ptb_context* ctx, int which, int kernel, uint64_t n, const flo
     REQUIRE_DEVICE(ctx);
     REQUIRE_BUILT(ctx);
     if (!hit) return ctx->fail(PTB_ERR_INVALID, "hit output is required");
-    if (which < 0 || which > 1 || kernel < 0 || kernel > 1) return ctx->fail(PTB_ERR_INVALID, "bad which/kernel");
+    if (which < 0 || which > 1 || kernel < 0 || kernel > 2) return ctx->fail(PTB_ERR_INVALID, "bad which/kernel");
     if (n == 0) return PTB_OK;
     int rc = ptb_trace_upload(ctx, n, o3, d3, tmax);
     if (rc != PTB_OK) return rc;
@@ -438,6 +438,7 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "tail_roles") ctx->opt_tail_roles = value;
     else if (n == "path_threshold") ctx->opt_path_threshold = value;
     else if (n == "shared_device") ctx->opt_shared_device = value ? 1 : 0;
+    else if (n == "stack_shared") ctx->opt_stack_shared = (value == 8 || value == 12 || value == 16) ? value : 0;
     else if (n == "thin_rays_per_lane") ctx->opt_thin_rays_per_lane = std::max(0, value);
     else if (n == "path_blocks") ctx->opt_path_blocks = std::max(4, std::min(6, value));
     else if (n == "finish_quorum") ctx->opt_finish_quorum = std::max(1, std::min(32, value));

@@ -246,7 +246,7 @@ struct ExtendJob
     }
 };
 
-template <int MB>
+template <int MB, int SSTACK = 0>
 __global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint32_t it, int sort, int refill_below, int node_quorum)
 {
     WfSet& S = Q.c->set[it % 3u];
@@ -257,7 +257,7 @@ __global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint
         if (n_cont + n_term) Q.c->stat_iters += 1;
     }
     ExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort};
-    persistent_trace<0>(V.S, job, &S.cur_extend, n_cont + n_term, refill_below, node_quorum);
+    persistent_trace<0, ExtendJob, false, SSTACK>(V.S, job, &S.cur_extend, n_cont + n_term, refill_below, node_quorum);
     const unsigned long long p = warp_sum(job.paths), q = warp_sum(job.settled);
     if ((threadIdx.x & 31u) == 0u && p) atomicAdd(&Q.c->stat_paths, p);
     if ((threadIdx.x & 31u) == 0u && q) atomicAdd(&Q.c->stat_settled, q);  // primary rays settled in start() without a traversal: counted apart
@@ -420,12 +420,12 @@ struct NeeJob
     }
 };
 
-template <int MB>
+template <int MB, int SSTACK = 0>
 __global__ void __launch_bounds__(128, MB) k_nee(RenderView V, Queues Q, uint32_t it, int refill_below, int node_quorum)
 {
     WfSet& S = Q.c->set[it % 3u];
     NeeJob job{V, Q};
-    persistent_trace<2>(V.S, job, &S.cur_nee, S.n_nee, refill_below, node_quorum);
+    persistent_trace<2, NeeJob, false, SSTACK>(V.S, job, &S.cur_nee, S.n_nee, refill_below, node_quorum);
     const unsigned long long a = warp_sum(job.n_shadow), b = warp_sum(job.n_probe), c = warp_sum(job.n_probe_shadow);
     if ((threadIdx.x & 31u) == 0u)
     {
@@ -1380,7 +1380,12 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             switch (eb)
             {
             case 5: k_extend<5><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
-            case 7: k_extend<7><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
+            case 7:
+                if (ctx->opt_stack_shared == 8) k_extend<7, 8><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq);
+                else if (ctx->opt_stack_shared == 12) k_extend<7, 12><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq);
+                else if (ctx->opt_stack_shared == 16) k_extend<7, 16><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq);
+                else k_extend<7><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq);
+                break;
             case 8: k_extend<8><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
             default: k_extend<6><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq); break;
             }
@@ -1402,7 +1407,12 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
                 {
                 case 4: k_nee<4><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
                 case 7: k_nee<7><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
-                case 8: k_nee<8><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
+                case 8:
+                    if (ctx->opt_stack_shared == 8) k_nee<8, 8><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq);
+                    else if (ctx->opt_stack_shared == 12) k_nee<8, 12><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq);
+                    else if (ctx->opt_stack_shared == 16) k_nee<8, 16><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq);
+                    else k_nee<8><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq);
+                    break;
                 case 6: k_nee<6><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
                 default: k_nee<5><<<ng, threads, 0, gs>>>(V, Q, it, rbn, nq); break;
                 }

@@ -197,6 +197,25 @@ PTB_HD void finish_hit(const SceneDev& S, V3 d_world, uint32_t inst, uint32_t pr
 // back) before its inner children are visited, TLAS leaves are stacked nearest-on-top: the visit order is that of the
 // nested-loop formulation this replaces.
 // ------------------------------------------------------------------------------------------------------------------------
+// Traversal stack access: a plain array (local memory on the device), or HybridStack — the first NS entries of every thread in
+// shared memory ([entry][thread], conflict-free 8-byte accesses), the rest in local memory (persist.cuh, `stack_shared` option).
+PTB_HD uint2 stk_get(const uint2* a, int i) { return a[i]; }
+PTB_HD void stk_set(uint2* a, int i, uint2 v) { a[i] = v; }
+template <int NS, int STRIDE>
+struct HybridStack
+{
+    uint2* sh;   // &shared[0][thread]
+    uint2* loc;  // entries NS.. in local memory
+};
+template <int NS, int STRIDE>
+PTB_HD uint2 stk_get(const HybridStack<NS, STRIDE>& h, int i) { return i < NS ? h.sh[i * STRIDE] : h.loc[i - NS]; }
+template <int NS, int STRIDE>
+PTB_HD void stk_set(const HybridStack<NS, STRIDE>& h, int i, uint2 v)
+{
+    if (i < NS) h.sh[i * STRIDE] = v;
+    else h.loc[i - NS] = v;
+}
+
 constexpr uint32_t TRAV_NONE = 0xffffffffu;
 struct WideTrav
 {
@@ -298,7 +317,8 @@ PTB_HD uint32_t popc32(uint32_t m)
 // MODE 0: closest hit, 1: any hit, 2: s.any decides at run time.  Returns false when the traversal is complete
 // (closest: s.hit_inst != TRAV_NONE tells whether something was hit; any: s.hit_inst != TRAV_NONE == occluded).
 // wide_step_pop: stage P.  Returns false when the traversal is complete (stack empty, nothing pending).
-PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, uint2* stack)
+template <class Stack>
+PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, Stack stack)
 {
     // ---- P: nothing pending -> next node from the current group, or pop ----------------------------------------------
     if (s.tri_i >= s.tri_end && s.lh == 0u && s.node == TRAV_NONE)
@@ -315,7 +335,7 @@ PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, uint2* stack)
                 s.ray.oi = s.oiw;
             }
             if (s.sp == 0) return false;
-            const uint2 e = stack[--s.sp];
+            const uint2 e = stk_get(stack, --s.sp);
             if (e.y & 0x80000000u)
             {
                 // TLAS leaf (tlas.rs:88-100 / :132-139): exact leaf box with the current t_max, then Ray::transform
@@ -353,7 +373,7 @@ PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, uint2* stack)
             const uint32_t sl = (uint32_t)p ^ s.ray.oi;
             s.node = s.G.x + popc32(imask & ((1u << sl) - 1u));
             s.G.y &= ~(1u << p);
-            if (s.G.y & 0xffu) stack[s.sp++] = s.G;
+            if (s.G.y & 0xffu) stk_set(stack, s.sp++, s.G);
             s.G.y = 0u;
         }
     }
@@ -365,8 +385,8 @@ PTB_HD bool wide_has_leaf_work(const WideTrav& s) { return s.lh != 0u || s.tri_i
 // wide_step_work: stages N, L, T.  `allow_node` lets a warp postpone the (expensive) node stage until enough of its lanes
 // want it (persist.cuh); a lane whose node is postponed simply keeps it pending.  Returns false when an any-hit query is
 // decided.
-template <int MODE>
-PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, uint2* stack, bool allow_node)
+template <int MODE, class Stack>
+PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, Stack stack, bool allow_node)
 {
     const bool ANY = MODE == 2 ? (s.any != 0u) : (MODE == 1);
     // ---- N: fetch and test one wide node ---------------------------------------------------------------------------------
@@ -391,7 +411,7 @@ PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, uint2* stack, bool al
         else
         {
             // TLAS leaves: push the inner group first, then the instances far to near (nearest popped first)
-            if (s.G.y) { stack[s.sp++] = s.G; s.G.y = 0u; }
+            if (s.G.y) { stk_set(stack, s.sp++, s.G); s.G.y = 0u; }
             uint32_t m = lh;
             while (m)
             {
@@ -401,7 +421,7 @@ PTB_HD bool wide_step_work(WideTrav& s, const SceneDev& S, uint2* stack, bool al
                 uint2 e;
                 e.x = q1.y + popc32(lmask & ((1u << sl) - 1u));
                 e.y = 0x80000000u;
-                stack[s.sp++] = e;
+                stk_set(stack, s.sp++, e);
             }
         }
     }

@@ -69,8 +69,11 @@ def test_traversal_parity(ptb, po, scenes, name):
             got = ctx.trace_closest(o, d, tm, which=which, kernel=0)  # 8-wide persistent kernel
             ties += compare_closest(ref, got, sc, o, d, tm, which=which)[1]
             assert np.array_equal(ctx.trace_any(o, d, tm, which=which, kernel=0)["hit"], ref_any["hit"])
+            got = ctx.trace_closest(o, d, tm, which=which, kernel=2)  # team kernel: eight lanes per ray (csrc/team.cuh)
+            ties += compare_closest(ref, got, sc, o, d, tm, which=which)[1]
+            assert np.array_equal(ctx.trace_any(o, d, tm, which=which, kernel=2)["hit"], ref_any["hit"])
     print(f"{name}: wide-kernel ties = {ties}")
-    assert ties < 500
+    assert ties < 1000
 
 
 def test_traversal_golden(ptb, scenes):
@@ -429,6 +432,7 @@ def test_full_size_properties_c4(ptb, po, scenes):
     ctx = ptb.Context(0)
     ctx.upload(sd)
     sc = po.OracleScene(sd)
+    ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, sd.aspect)
     n = 1 << 20
     st = scenes.pixel_centre_st(sd.width, sd.height, stride=max(1, int((sd.width * sd.height / n) ** 0.5)))[:n]
     op, dp = ctx.camera_rays(st)
