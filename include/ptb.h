@@ -250,6 +250,21 @@ int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, floa
 int ptb_set_option(ptb_context* ctx, const char* name, int value);
 
 
+/* ---- allocation-free variant of ptb_trace_closest ---------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that must not allocate device memory
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same arguments (host arrays), same 8-wide
+ * persistent kernel (kernel = 0) and bit-identical results as ptb_trace_closest, but the call makes NO cudaMalloc / cudaFree or other
+ * allocating call: the staged rays, the staged results and the kernel's work cursor live in one file-scope device array of
+ * PTB_STATIC_SCRATCH_BYTES (csrc/noalloc.cu) that every GPU which loads the library holds until the process exits.
+ * Limits: n <= PTB_STATIC_TRACE_MAX_RAYS, otherwise PTB_ERR_INVALID with a message naming the limit.  All calls on a device share the
+ * array, which keeps the previous call's contents (the call clears what must start at zero): calls that overlap on one GPU — two
+ * contexts, threads or processes — race and must be serialised by the caller.  The scene must be built (ptb_build allocates; do
+ * that outside the allocation-free region). */
+#define PTB_STATIC_TRACE_MAX_RAYS 65536
+#define PTB_STATIC_SCRATCH_BYTES 4325632
+int ptb_trace_closest_static(ptb_context* ctx, int which, uint64_t n, const float* o3, const float* d3, const float* tmax, uint8_t* hit, float* t, float* u, float* v,
+                             uint32_t* prim, uint32_t* blas, uint32_t* inst, uint8_t* front, float* normal3);
+
 /* ---- load_obj  blas.rs:44-131 ---------------------------------------------------------------------------------------------
  * The reference's only on-disk input: an OBJ file -> the triangle vertex array ptb_scene_upload takes (ntri * 3 vertices x
  * (position xyz, normal xyz)), with load_obj's rules: `v` / `vn` / `f` lines only, 1-based indices (negative = from the end), `vn`

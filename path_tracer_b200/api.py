@@ -33,8 +33,9 @@ EXPORTS = [
     "ptb_group_create", "ptb_group_unique_id", "ptb_group_join", "ptb_group_destroy", "ptb_group_last_error", "ptb_group_size", "ptb_group_context",
     "ptb_group_sample_range", "ptb_group_scene_upload", "ptb_group_build", "ptb_group_set_camera", "ptb_group_set_option", "ptb_group_frame_begin",
     "ptb_group_render", "ptb_group_reduce", "ptb_group_read_accum", "ptb_group_read_aux", "ptb_group_get_counters", "ptb_group_reset_counters",
-    "ptb_group_reduce_ms", "ptb_load_obj", "ptb_load_obj_text", "ptb_load_obj_error", "ptb_free",
+    "ptb_group_reduce_ms", "ptb_load_obj", "ptb_load_obj_text", "ptb_load_obj_error", "ptb_free", "ptb_trace_closest_static",
 ]
+STATIC_TRACE_MAX_RAYS = 65536  # PTB_STATIC_TRACE_MAX_RAYS
 # ptb_get_counters: [0] extend rays that ran a traversal, [7] primary rays settled by the bounds pre-test without one (k_extend)
 COUNTER_NAMES = ["extend", "shadow", "probe", "paths", "iterations", "launches", "extend_path", "settled"]
 
@@ -226,6 +227,16 @@ class Context:
                    blas=np.zeros(n, np.uint32), inst=np.zeros(n, np.uint32), front=np.zeros(n, np.uint8), normal=np.zeros((n, 3), np.float32))
         self._ck(self.L.ptb_trace_closest(self.h, which, kernel, C.c_uint64(n), _p(o), _p(d), _p(tmax), _p(out["hit"]), _p(out["t"]), _p(out["u"]), _p(out["v"]),
                                           _p(out["prim"]), _p(out["blas"]), _p(out["inst"]), _p(out["front"]), _p(out["normal"])))
+        return out
+
+    def trace_closest_static(self, o, d, tmax, which=0):
+        """ptb_trace_closest_static: the same batch trace without any device allocation (static scratch, <= STATIC_TRACE_MAX_RAYS rays)."""
+        n = o.shape[0]
+        o, d, tmax = (np.ascontiguousarray(x, np.float32) for x in (o, d, tmax))
+        out = dict(hit=np.zeros(n, np.uint8), t=np.zeros(n, np.float32), u=np.zeros(n, np.float32), v=np.zeros(n, np.float32), prim=np.zeros(n, np.uint32),
+                   blas=np.zeros(n, np.uint32), inst=np.zeros(n, np.uint32), front=np.zeros(n, np.uint8), normal=np.zeros((n, 3), np.float32))
+        self._ck(self.L.ptb_trace_closest_static(self.h, which, C.c_uint64(n), _p(o), _p(d), _p(tmax), _p(out["hit"]), _p(out["t"]), _p(out["u"]), _p(out["v"]),
+                                                 _p(out["prim"]), _p(out["blas"]), _p(out["inst"]), _p(out["front"]), _p(out["normal"])))
         return out
 
     def trace_any(self, o, d, tmax, which=0, kernel=0):

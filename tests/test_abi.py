@@ -79,3 +79,14 @@ def test_validation_errors_mirror_reference_panics(scenes):
     # the Python mirror asserts like Model::new
     with pytest.raises(AssertionError):
         ptb.Model(sd.verts[:2], ptb.Lambertian.new((1, 1, 1)), [(2.0, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0)])
+
+
+def test_static_scratch_entry_point_refuses_without_device(scenes):
+    import path_tracer_b200 as ptb
+    ctx = ptb.Context(-1)
+    sd = scenes.scene_c2()
+    ctx.upload(sd)
+    o, d, tm = scenes.incoherent_rays(sd, 8)
+    with pytest.raises(ptb.PtbError) as e:
+        ctx.trace_closest_static(o, d, tm)
+    assert e.value.code == ptb.api.PTB_ERR_NO_DEVICE
