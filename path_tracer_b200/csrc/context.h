@@ -42,6 +42,12 @@ struct TemporalState;
 
 }  // namespace ptb
 
+// options of the multiray kernels (multiray.cuh): finished / idle ray slots of a warp that trigger a finish + start pass, lanes that must
+// hold a ray waiting for the node / leaf-triangle / instance stage before the warp runs it, resident blocks per SM (0 = what fits)
+struct MrOpts
+{
+    int free_quorum = 24, qn = 16, ql = 12, qi = 12, blocks_per_sm = 0;
+};
 struct ptb_context
 {
     int device = -1;
@@ -84,6 +90,7 @@ struct ptb_context
     int opt_block_threads = 128;
     int opt_blocks_per_sm = 8;
     int opt_refill_below = 8, opt_nee_refill_below = 8;    // persistent kernels refill idle lanes when fewer than this many lanes of a warp are traversing
+    MrOpts opt_mr;                // multiray kernels (mr_free_quorum, mr_qn, mr_ql, mr_qi, mr_blocks)
     int opt_node_quorum = 8;      // lanes of a warp that must want the node stage before it runs (1 = never postponed)
     int opt_extend_blocks = 7, opt_nee_blocks = 8;  // resident blocks per SM (launch bounds -> register cap) of k_extend / k_nee
     int opt_slots_per_pixel = 16;  // path slots per pixel (1..16): more slots = more paths in flight, fewer and larger wavefront iterations
@@ -158,5 +165,6 @@ struct TraceArgs
     float* normal;
     unsigned long long* counter;
 };
-cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream, int refill_below, int node_quorum);
+cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream, int refill_below, int node_quorum,
+                         const MrOpts& mo = MrOpts());
 }  // namespace ptb

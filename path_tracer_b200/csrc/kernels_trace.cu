@@ -5,6 +5,7 @@
 #include "context.h"
 #include "persist.cuh"
 #include "team.cuh"
+#include "multiray.cuh"
 
 namespace ptb {
 
@@ -145,8 +146,77 @@ __global__ void __launch_bounds__(128) trace_team_kernel(SceneDev S, int which, 
     }
 }
 
-cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream, int refill_below, int node_quorum)
+// multiray kernels (kernel = 3 / 4 / 5: two / three / four rays per lane; 6: one ray per lane, i.e. the cost of the shared-memory ray
+// records alone): multiray.cuh
+template <bool ANY>
+struct MrTraceJob
 {
+    static constexpr int JOBW = 1;
+    const SceneDev& S;
+    const TraceArgs& a;
+    int which;
+    unsigned long long base;
+    template <class R>
+    __device__ __forceinline__ uint32_t start(uint32_t idx, const R& r)
+    {
+        const unsigned long long i = base + idx;
+        r.st(MR_JOB, idx);
+        return mr_begin(r, S, which, ex::v3(a.o[i * 3], a.o[i * 3 + 1], a.o[i * 3 + 2]), ex::v3(a.d[i * 3], a.d[i * 3 + 1], a.d[i * 3 + 2]), a.tmax[i], ANY);
+    }
+    template <class R>
+    __device__ __forceinline__ uint32_t finish(const R& r, bool mine)
+    {
+        if (!mine) return MT_IDLE;
+        Hit h;
+        h.t = r.ldf(MR_TMAX); h.u = mr_hit_u(r); h.v = mr_hit_v(r); h.slot_or_prim = r.ld(MR_HSLOT); h.inst = r.ld(MR_HINST);
+        write_result(S, which, a, base + r.ld(MR_JOB), ANY, h.inst != TRAV_NONE, h, 1u, r.ld3(MR_WD));
+        return MT_IDLE;
+    }
+};
+
+template <bool ANY, int K>
+__global__ void __launch_bounds__(128) trace_mr_kernel(SceneDev S, int which, unsigned long long base, uint32_t n, TraceArgs a, MrOpts mo)
+{
+    MrTraceJob<ANY> job{S, a, which, base};
+    mr_persistent_trace<ANY ? 1 : 0, K>(S, job, (uint32_t*)a.counter, n, mo.free_quorum, mo.qn, mo.ql, mo.qi);
+}
+
+template <bool ANY, int K>
+static cudaError_t launch_mr(const SceneDev& S, int which, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream, const MrOpts& mo)
+{
+    const size_t smem = (size_t)K * (MR_JOB + MrTraceJob<ANY>::JOBW) * 128 * sizeof(uint32_t);
+    auto kern = trace_mr_kernel<ANY, K>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem);
+    if (e != cudaSuccess) return e;
+    if (mo.blocks_per_sm > 0) per_sm = std::min(per_sm, mo.blocks_per_sm);
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    for (uint64_t base = 0; base < n; base += 0x40000000ull)
+    {
+        e = cudaMemsetAsync(a.counter, 0, sizeof(unsigned long long), stream);
+        if (e != cudaSuccess) return e;
+        const uint32_t cnt = (uint32_t)std::min<uint64_t>(n - base, 0x40000000ull);
+        kern<<<sm_count * per_sm, 128, smem, stream>>>(S, which, base, cnt, a, mo);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trace(const SceneDev& S, int which, int kernel, int any_hit, uint64_t n, const TraceArgs& a, int sm_count, cudaStream_t stream, int refill_below, int node_quorum, const MrOpts& mo)
+{
+    if (kernel >= 3)
+    {
+        MrOpts m = mo;
+        if (m.free_quorum <= 0) m.free_quorum = 24;
+        switch (kernel)
+        {
+        case 3: return any_hit ? launch_mr<true, 2>(S, which, n, a, sm_count, stream, m) : launch_mr<false, 2>(S, which, n, a, sm_count, stream, m);
+        case 4: return any_hit ? launch_mr<true, 3>(S, which, n, a, sm_count, stream, m) : launch_mr<false, 3>(S, which, n, a, sm_count, stream, m);
+        case 5: return any_hit ? launch_mr<true, 4>(S, which, n, a, sm_count, stream, m) : launch_mr<false, 4>(S, which, n, a, sm_count, stream, m);
+        default: return any_hit ? launch_mr<true, 1>(S, which, n, a, sm_count, stream, m) : launch_mr<false, 1>(S, which, n, a, sm_count, stream, m);
+        }
+    }
     const int blocks = sm_count * 8;
     if (kernel == 0)
     {

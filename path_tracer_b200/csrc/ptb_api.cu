@@ -347,14 +347,14 @@ int ptb_trace_resident(ptb_context* ctx, int which, int kernel, int any_hit, int
     REQUIRE_DEVICE(ctx);
     REQUIRE_BUILT(ctx);
     if (ctx->t_n == 0) return ctx->fail(PTB_ERR_INVALID, "no resident ray batch: call ptb_trace_upload");
-    if (which < 0 || which > 1 || kernel < 0 || kernel > 2 || repeats < 1) return ctx->fail(PTB_ERR_INVALID, "bad arguments");
+    if (which < 0 || which > 1 || kernel < 0 || kernel > 6 || repeats < 1) return ctx->fail(PTB_ERR_INVALID, "bad arguments");
     PTB_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaEvent_t e0, e1;
     PTB_CUDA(ctx, cudaEventCreate(&e0));
     PTB_CUDA(ctx, cudaEventCreate(&e1));
     TraceArgs a = trace_args(ctx);
     PTB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
-    for (int r = 0; r < repeats; ++r) PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, any_hit, ctx->t_n, a, ctx->sm_count, ctx->stream, any_hit ? ctx->opt_nee_refill_below : ctx->opt_refill_below, ctx->opt_node_quorum));
+    for (int r = 0; r < repeats; ++r) PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, any_hit, ctx->t_n, a, ctx->sm_count, ctx->stream, any_hit ? ctx->opt_nee_refill_below : ctx->opt_refill_below, ctx->opt_node_quorum, ctx->opt_mr));
     PTB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
     PTB_CUDA(ctx, cudaEventSynchronize(e1));
     float ms = 0;
@@ -385,11 +385,11 @@ int ptb_trace_closest(ptb_context* ctx, int which, int kernel, uint64_t n, const
     REQUIRE_DEVICE(ctx);
     REQUIRE_BUILT(ctx);
     if (!hit) return ctx->fail(PTB_ERR_INVALID, "hit output is required");
-    if (which < 0 || which > 1 || kernel < 0 || kernel > 2) return ctx->fail(PTB_ERR_INVALID, "bad which/kernel");
+    if (which < 0 || which > 1 || kernel < 0 || kernel > 6) return ctx->fail(PTB_ERR_INVALID, "bad which/kernel");
     if (n == 0) return PTB_OK;  // empty batch
     int rc = ptb_trace_upload(ctx, n, o3, d3, tmax);
     if (rc != PTB_OK) return rc;
-    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 0, n, trace_args(ctx), ctx->sm_count, ctx->stream, ctx->opt_refill_below, ctx->opt_node_quorum));
+    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 0, n, trace_args(ctx), ctx->sm_count, ctx->stream, ctx->opt_refill_below, ctx->opt_node_quorum, ctx->opt_mr));
 #define DL(dst, src, bytes) \
     if (dst) PTB_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream))
     DL(hit, ctx->t_hit.p, n);
@@ -411,11 +411,11 @@ int ptb_trace_any(ptb_context* ctx, int which, int kernel, uint64_t n, const flo
     REQUIRE_DEVICE(ctx);
     REQUIRE_BUILT(ctx);
     if (!hit) return ctx->fail(PTB_ERR_INVALID, "hit output is required");
-    if (which < 0 || which > 1 || kernel < 0 || kernel > 2) return ctx->fail(PTB_ERR_INVALID, "bad which/kernel");
+    if (which < 0 || which > 1 || kernel < 0 || kernel > 6) return ctx->fail(PTB_ERR_INVALID, "bad which/kernel");
     if (n == 0) return PTB_OK;
     int rc = ptb_trace_upload(ctx, n, o3, d3, tmax);
     if (rc != PTB_OK) return rc;
-    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 1, n, trace_args(ctx), ctx->sm_count, ctx->stream, ctx->opt_nee_refill_below, ctx->opt_node_quorum));
+    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 1, n, trace_args(ctx), ctx->sm_count, ctx->stream, ctx->opt_nee_refill_below, ctx->opt_node_quorum, ctx->opt_mr));
     PTB_CUDA(ctx, cudaMemcpyAsync(hit, ctx->t_hit.p, n, cudaMemcpyDeviceToHost, ctx->stream));
     PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return PTB_OK;
@@ -431,6 +431,11 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "block_threads") ctx->opt_block_threads = value;
     else if (n == "blocks_per_sm") ctx->opt_blocks_per_sm = value;
     else if (n == "node_quorum") ctx->opt_node_quorum = value;
+    else if (n == "mr_free_quorum") ctx->opt_mr.free_quorum = value;
+    else if (n == "mr_qn") ctx->opt_mr.qn = value;
+    else if (n == "mr_ql") ctx->opt_mr.ql = value;
+    else if (n == "mr_qi") ctx->opt_mr.qi = value;
+    else if (n == "mr_blocks") ctx->opt_mr.blocks_per_sm = value;
     else if (n == "extend_blocks") ctx->opt_extend_blocks = value;
     else if (n == "nee_blocks") ctx->opt_nee_blocks = value;
     else if (n == "slots_per_pixel") ctx->opt_slots_per_pixel = value;

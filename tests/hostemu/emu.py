@@ -57,6 +57,17 @@ class EmuScene:
         return out
 
 
+def trace_mr(es, o, d, tmax, which=0, any_hit=False, K=3, free_quorum=24, qn=16, ql=12, qi=12):
+    """multiray.cuh (K rays per lane, gated stages) on one emulated warp; returns hit/t/u/v/prim/inst and the stage statistics"""
+    n = o.shape[0]
+    o, d, tmax = (np.ascontiguousarray(x, np.float32) for x in (o, d, tmax))
+    out = dict(hit=np.zeros(n, np.uint8), t=np.zeros(n, np.float32), u=np.zeros(n, np.float32), v=np.zeros(n, np.float32), prim=np.zeros(n, np.uint32),
+               inst=np.zeros(n, np.uint32), stats=np.zeros(8, np.uint64))
+    lib().emu_trace_mr(C.c_void_p(es.h), which, int(any_hit), C.c_uint64(n), _p(o), _p(d), _p(tmax), K, free_quorum, qn, ql, qi, _p(out["hit"]), _p(out["t"]), _p(out["u"]),
+                       _p(out["v"]), _p(out["prim"]), _p(out["inst"]), _p(out["stats"]))
+    return out
+
+
 def camera(origin, target, fov_deg, aspect):
     m = np.zeros(16, np.float32)
     eye = np.zeros(3, np.float32)

@@ -11,6 +11,7 @@
 #include "../../path_tracer_b200/csrc/camera_host.h"
 #include "../../path_tracer_b200/csrc/host_scene.h"
 #include "../../path_tracer_b200/csrc/traverse.h"
+#include "../../path_tracer_b200/csrc/multiray.cuh"
 #include "../../path_tracer_b200/csrc/temporal.cuh"
 #include "../../path_tracer_b200/csrc/wavefront.h"
 
@@ -209,4 +210,110 @@ void emu_state_update(int W, int H, const float* data, const float* position, co
         }
 }
 void emu_camera(const float* origin, const float* target, float fov_deg, float aspect, float* m16, float* eye3) { camera_setup(origin, target, fov_deg, aspect, m16, eye3); }
+}
+
+// K rays per lane with stage gating (multiray.cuh): one emulated warp of 32 lanes walks the batch with the loop structure of
+// mr_persistent_trace — the stage functions are the product's own, the ballots are loops over the lanes.
+template <int K>
+static void emu_mr_warp(const SceneDev& S, int which, int any, uint64_t n, const float* o, const float* d, const float* tmax, int free_quorum, int qn, int ql, int qi,
+                        uint8_t* hit, float* t, float* u, float* v, uint32_t* slot, uint32_t* inst, uint64_t* stats)
+{
+    constexpr int NW = MR_JOB + 1;
+    using R = MrRay<1>;
+    std::vector<uint32_t> mem((size_t)32 * K * NW, 0u);
+    std::vector<uint2> stk((size_t)32 * K * WIDE_STACK_CAP);
+    uint32_t tags[32] = {};
+    auto ray = [&](int lane, int k) { return R{mem.data() + ((size_t)lane * K + k) * NW}; };
+    auto stack = [&](int lane, int k) { return stk.data() + ((size_t)lane * K + k) * WIDE_STACK_CAP; };
+    uint64_t next = 0;
+    for (;;)
+    {
+        int n_done = 0, n_idle = 0;
+        for (int l = 0; l < 32; ++l) { n_done += mr_count2<K>(tags[l], MT_DONE, MT_DONE); n_idle += mr_count2<K>(tags[l], MT_IDLE, MT_IDLE); }
+        const int n_act = 32 * K - n_done - n_idle;
+        const bool more = next < n;
+        if (more ? (n_done + n_idle >= free_quorum) : (n_done > 0 && (n_done >= 8 || n_act == 0)))
+        {
+            for (int l = 0; l < 32; ++l)
+            {
+                const int k = mr_first<K>(tags[l], MT_DONE);
+                if (k < 0) continue;
+                const R r = ray(l, k);
+                const uint64_t i = r.ld(MR_JOB);
+                const bool f = mr_hit(r);
+                hit[i] = f;
+                if (!any)
+                {
+                    t[i] = f ? r.ldf(MR_TMAX) : ex::inf();
+                    u[i] = f ? mr_hit_u(r) : 0.0f;
+                    v[i] = f ? mr_hit_v(r) : 0.0f;
+                    slot[i] = f ? r.ld(MR_HSLOT) : 0xffffffffu;
+                    inst[i] = f ? r.ld(MR_HINST) : 0xffffffffu;
+                }
+                tags[l] = mr_set(tags[l], k, MT_IDLE);
+            }
+            for (int pass = 0; pass < K && next < n; ++pass)
+                for (int l = 0; l < 32 && next < n; ++l)
+                {
+                    const int k = mr_first<K>(tags[l], MT_IDLE);
+                    if (k < 0) continue;
+                    const uint64_t i = next++;
+                    const R r = ray(l, k);
+                    r.st(MR_JOB, (uint32_t)i);
+                    tags[l] = mr_set(tags[l], k, mr_begin(r, S, which, ex::v3(o[i * 3], o[i * 3 + 1], o[i * 3 + 2]), ex::v3(d[i * 3], d[i * 3 + 1], d[i * 3 + 2]), tmax[i], any != 0));
+                }
+        }
+        bool live = false;
+        for (int l = 0; l < 32; ++l) live |= tags[l] != 0u;
+        if (!live) { if (next >= n) break; continue; }
+        if (stats) stats[0]++;
+        for (int l = 0; l < 32; ++l)
+        {
+            const int k = mr_first<K>(tags[l], MT_P);
+            if (k >= 0) tags[l] = mr_set(tags[l], k, mr_stage_p(ray(l, k), stack(l, k)));
+        }
+        int cn = 0, cl = 0, ci = 0;
+        for (int l = 0; l < 32; ++l) { cn += mr_has<K>(tags[l], MT_N); cl += mr_has2<K>(tags[l], MT_L, MT_T); ci += mr_has<K>(tags[l], MT_I); }
+        bool run_n = cn >= qn, run_l = cl >= ql, run_i = ci >= qi;
+        if (!(run_n && cn) && !(run_l && cl) && !(run_i && ci)) run_n = run_l = run_i = true;
+        if (stats) { stats[1] += run_n && cn; stats[2] += run_n ? cn : 0; stats[3] += run_l && cl; stats[4] += run_l ? cl : 0; stats[5] += run_i && ci; stats[6] += run_i ? ci : 0; }
+        for (int l = 0; l < 32; ++l)
+        {
+            if (run_i)
+            {
+                const int k = mr_first<K>(tags[l], MT_I);
+                if (k >= 0) tags[l] = mr_set(tags[l], k, mr_stage_i(ray(l, k), S));
+            }
+            if (run_n)
+            {
+                const int k = mr_first<K>(tags[l], MT_N);
+                if (k >= 0) tags[l] = mr_set(tags[l], k, mr_stage_n(ray(l, k), S, stack(l, k)));
+            }
+            if (run_l)
+            {
+                int k = mr_first<K>(tags[l], MT_L);
+                uint32_t tag = MT_L;
+                if (k < 0) { k = mr_first<K>(tags[l], MT_T); tag = MT_T; }
+                if (k >= 0) tags[l] = mr_set(tags[l], k, mr_stage_lt<2>(ray(l, k), S, tag));
+            }
+        }
+    }
+}
+
+extern "C" void emu_trace_mr(void* h, int which, int any, uint64_t n, const float* o, const float* d, const float* tmax, int K, int free_quorum, int qn, int ql, int qi,
+                             uint8_t* hit, float* t, float* u, float* v, uint32_t* prim, uint32_t* inst, uint64_t* stats)
+{
+    const HostScene& sc = *(HostScene*)h;
+    const SceneDev S = host_view(sc);
+    std::vector<uint32_t> slot(n), gi(n);
+    if (K == 1) emu_mr_warp<1>(S, which, any, n, o, d, tmax, free_quorum, qn, ql, qi, hit, t, u, v, slot.data(), gi.data(), stats);
+    else if (K == 2) emu_mr_warp<2>(S, which, any, n, o, d, tmax, free_quorum, qn, ql, qi, hit, t, u, v, slot.data(), gi.data(), stats);
+    else if (K == 3) emu_mr_warp<3>(S, which, any, n, o, d, tmax, free_quorum, qn, ql, qi, hit, t, u, v, slot.data(), gi.data(), stats);
+    else emu_mr_warp<4>(S, which, any, n, o, d, tmax, free_quorum, qn, ql, qi, hit, t, u, v, slot.data(), gi.data(), stats);
+    if (any) return;
+    for (uint64_t i = 0; i < n; ++i)
+    {
+        prim[i] = hit[i] ? S.tri_prim[slot[i]] : 0xffffffffu;
+        inst[i] = hit[i] ? gi[i] - S.tlas[which].inst_base : 0xffffffffu;
+    }
 }
