@@ -124,7 +124,9 @@ int ptb_bvh_stats(ptb_context* ctx, uint64_t out[8]);
 /* ---- fixed ray batches: TLAS::intersect (tlas.rs:66-110) / TLAS::any_intersect (tlas.rs:111-144) ---------------
  * which: 0 = scene.world, 1 = scene.lights.  kernel: 0 = 8-wide persistent kernel (the renderer's), 1 = reference-order
  * binary kernel (walks the reference's own binary BVH in the reference's visit order; bit-exact incl. ties), 2 = team kernel
- * (eight lanes per ray over the 8-wide layout, csrc/team.cuh; same results as kernel 0 up to the resolution of exact ties).
+ * (eight lanes per ray over the 8-wide layout, csrc/team.cuh; same results as kernel 0 up to the resolution of exact ties),
+ * 3 / 4 / 5 = multiray kernels (two / three / four rays per lane with gated stages and the ray records in shared memory,
+ * csrc/multiray.cuh; 6 = the same machinery with one ray per lane): bit-identical to kernel 0.
  * o3/d3: n*3 floats (d normalised, ray.rs:12), tmax: n floats.  Host pointers; copies happen inside the call.
  * Outputs may be NULL except `hit`.  blas = scene blas index, inst = instance ordinal (`Model`x`matrices` order),
  * normal = world-space ray-facing shading normal (primitive.rs:161-165, tlas.rs:103-105). */
@@ -230,6 +232,12 @@ int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, floa
  *   extend_blocks, nee_blocks   resident blocks per SM (= register cap) of k_extend (5..8, default 7) / k_nee (4..8, default 8)
  *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit 8, any-hit 8)
  *   node_quorum       lanes that must want the node stage before it runs (default 8)
+ *   multiray          rays per lane of k_extend / k_nee: 0 one (persist.cuh), 2 / 3 the multiray kernels (csrc/multiray.cuh: a lane owns
+ *                     K rays, the thin stages run once enough lanes hold a ray waiting for them), < 0 automatic (default): 2 for scenes
+ *                     of >= 384 wide nodes.  Same results bit for bit.  mr_qn / mr_ql / mr_qi (12 / 8 / 8): lanes that must hold a ray
+ *                     waiting for the node / leaf / instance stage before a warp runs it; mr_free_quorum (24): finished or idle ray
+ *                     slots of a warp that trigger a refill; mr_blocks: resident blocks per SM (0 = what fits); mr_min_per_lane (16):
+ *                     iterations with fewer live slots per lane of the one-ray grid run the one-ray kernels
  *   tail_threshold    active slots at which the wavefront loop hands the remaining slots to the single-launch tail kernel
  *                     (< 0 automatic = 2.5 x the resident slot capacity of that kernel, 0 = never)
  *   tail_roles        1 (default): the tail kernel runs shadow ray, light probe and the next bounce's ray of a slot on three warps

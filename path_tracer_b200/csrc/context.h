@@ -46,7 +46,7 @@ struct TemporalState;
 // hold a ray waiting for the node / leaf-triangle / instance stage before the warp runs it, resident blocks per SM (0 = what fits)
 struct MrOpts
 {
-    int free_quorum = 24, qn = 16, ql = 12, qi = 12, blocks_per_sm = 0;
+    int free_quorum = 24, qn = 12, ql = 8, qi = 8, blocks_per_sm = 0;
 };
 struct ptb_context
 {
@@ -90,6 +90,8 @@ struct ptb_context
     int opt_block_threads = 128;
     int opt_blocks_per_sm = 8;
     int opt_refill_below = 8, opt_nee_refill_below = 8;    // persistent kernels refill idle lanes when fewer than this many lanes of a warp are traversing
+    int opt_multiray = -1;        // rays per lane of k_extend / k_nee: 0 = one (persist.cuh), 2 / 3 = multiray.cuh, -1 = by scene size (render.cu)
+    int opt_mr_min_per_lane = 16; // multiray kernels only while the live slots are at least this many per lane of the one-ray grid
     MrOpts opt_mr;                // multiray kernels (mr_free_quorum, mr_qn, mr_ql, mr_qi, mr_blocks)
     int opt_node_quorum = 8;      // lanes of a warp that must want the node stage before it runs (1 = never postponed)
     int opt_extend_blocks = 7, opt_nee_blocks = 8;  // resident blocks per SM (launch bounds -> register cap) of k_extend / k_nee

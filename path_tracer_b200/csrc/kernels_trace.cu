@@ -164,12 +164,21 @@ struct MrTraceJob
         return mr_begin(r, S, which, ex::v3(a.o[i * 3], a.o[i * 3 + 1], a.o[i * 3 + 2]), ex::v3(a.d[i * 3], a.d[i * 3 + 1], a.d[i * 3 + 2]), a.tmax[i], ANY);
     }
     template <class R>
+    __device__ __forceinline__ void world_ray(const R& r, V3* o, V3* d) const
+    {
+        const unsigned long long i = base + r.ld(MR_JOB);
+        *o = ex::v3(a.o[i * 3], a.o[i * 3 + 1], a.o[i * 3 + 2]);
+        *d = ex::v3(a.d[i * 3], a.d[i * 3 + 1], a.d[i * 3 + 2]);
+    }
+    template <class R>
     __device__ __forceinline__ uint32_t finish(const R& r, bool mine)
     {
         if (!mine) return MT_IDLE;
         Hit h;
         h.t = r.ldf(MR_TMAX); h.u = mr_hit_u(r); h.v = mr_hit_v(r); h.slot_or_prim = r.ld(MR_HSLOT); h.inst = r.ld(MR_HINST);
-        write_result(S, which, a, base + r.ld(MR_JOB), ANY, h.inst != TRAV_NONE, h, 1u, r.ld3(MR_WD));
+        V3 o, d;
+        world_ray(r, &o, &d);
+        write_result(S, which, a, base + r.ld(MR_JOB), ANY, h.inst != TRAV_NONE, h, 1u, d);
         return MT_IDLE;
     }
 };

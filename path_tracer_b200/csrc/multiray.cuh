@@ -5,7 +5,7 @@
 // in the stage its ray is at.  A node test hands 0.23 leaves to a lane on average, so L / T / I run at 4-5 of 32 lanes however the
 // node stage is gated (profiles/r2m_c3_extend_sass_blocks.txt): a third of the warp instructions at an eighth of the width.  Making
 // a lane WAIT for a fuller stage costs as much as it saves when the lane has nothing else to do (measured in round 1).  Here a lane
-// owns K rays; a stage runs for the first of the lane's rays that wants it, and the thin stages (I, L/T) run only once enough lanes
+// owns K rays; a stage runs for the first of the lane's rays that wants it, and the thin stages (I, L) run only once enough lanes
 // of the warp hold a ray waiting for them — meanwhile those lanes go on with their other rays.  SIMT cost model on C3's rays
 // (tools/mrsim.py, calibrated against the capture above): K = 3-4 with quorums 16 / 12 / 12 needs 1.32-1.37 x fewer warp
 // instructions per bounce ray, 1.2-1.3 x for primary and shadow rays, overheads of the shared-memory state included.
@@ -19,22 +19,22 @@
 
 namespace ptb {
 
-// words of a ray record
+// words of a ray record (25 with one job word: 100 bytes per ray; the world-space origin and direction are not kept — they are re-read
+// from the job's own source when the ray leaves an instance, Job::world_ray)
 enum : int
 {
-    MR_WO = 0, MR_WD = 3, MR_INVW = 6,   // world-space ray and its exact reciprocal (ray.rs:1-8)
-    MR_O = 9, MR_D = 12, MR_INV = 15,    // current space: world, or BLAS space after Ray::transform
-    MR_TMAX = 18,
-    MR_NODE = 19,                        // tag N: wide node to fetch; tag I: leaf-header index of the TLAS leaf; tags L / T: leaf_base of the current node
-    MR_GX = 20, MR_GY = 21,              // inner children of the current node still to visit
-    MR_SP = 22,                          // sp | blas_sp << 8
-    MR_INST = 23,                        // InstanceRow index while inside a BLAS
-    MR_FL = 24,                          // lh | lmask << 8 | oi << 16 | oiw << 19 | any << 22 | in_blas << 23
-    MR_TRI = 25, MR_TEND = 26, MR_TENTER = 27,
-    MR_HUD = 28, MR_HVD = 29, MR_HDET = 30, MR_HSLOT = 31, MR_HINST = 32,
-    MR_JOB = 33                          // first word of the job's own per-ray data
+    MR_O = 0, MR_D = 3, MR_INV = 6,      // current space: world, or BLAS space after Ray::transform; exact reciprocal (ray.rs:1-8)
+    MR_TMAX = 9,
+    MR_NODE = 10,                        // tag N: wide node to fetch; tag I: leaf-header index of the TLAS leaf; tag L: leaf_base of the current node
+    MR_GX = 11, MR_GY = 12,              // inner children of the current node still to visit
+    MR_SP = 13,                          // sp | blas_sp << 8
+    MR_INST = 14,                        // InstanceRow index while inside a BLAS
+    MR_FL = 15,                          // lh | lmask << 8 | oi << 16 | oiw << 19 | any << 22 | in_blas << 23
+    MR_HUD = 16, MR_HVD = 17, MR_HDET = 18, MR_HSLOT = 19, MR_HINST = 20,
+    MR_INVW = 21,                        // exact reciprocal of the world-space direction
+    MR_JOB = 24                          // first word of the job's own per-ray data
 };
-enum : uint32_t { MT_IDLE = 0, MT_P = 1, MT_N = 2, MT_L = 3, MT_T = 4, MT_I = 5, MT_DONE = 6 };
+enum : uint32_t { MT_IDLE = 0, MT_P = 1, MT_N = 2, MT_L = 3, MT_I = 4, MT_DONE = 5 };
 constexpr uint32_t MR_FL_ANY = 1u << 22, MR_FL_BLAS = 1u << 23;
 
 // one ray record: word w at q[w * STRIDE]
@@ -79,22 +79,25 @@ PTB_HD int mr_count2(uint32_t tags, uint32_t x, uint32_t y)
 PTB_HD uint32_t mr_set(uint32_t tags, int k, uint32_t t) { return (tags & ~(7u << (3 * k))) | (t << (3 * k)); }
 
 // wide_begin: returns the ray's first tag
+// keep_hit: a follow-up any-hit traversal that leaves the previous closest hit's (ud, vd, det, slot) in place (an any-hit query only
+// writes MR_HINST)
 template <class R>
-PTB_HD uint32_t mr_begin(const R& r, const SceneDev& S, int which, V3 o, V3 d, float t_max, bool any)
+PTB_HD uint32_t mr_begin(const R& r, const SceneDev& S, int which, V3 o, V3 d, float t_max, bool any, bool keep_hit = false)
 {
     TravRay tr;
     set_ray(tr, o, d);
-    r.st3(MR_WO, o); r.st3(MR_WD, d); r.st3(MR_INVW, tr.inv);
-    r.st3(MR_O, o); r.st3(MR_D, d); r.st3(MR_INV, tr.inv);
+    r.st3(MR_O, o); r.st3(MR_D, d); r.st3(MR_INV, tr.inv); r.st3(MR_INVW, tr.inv);
     r.stf(MR_TMAX, t_max);
     r.st(MR_NODE, S.tlas[which].wide_root);
-    r.st(MR_GX, 0u); r.st(MR_GY, 0u);
+    r.st(MR_GY, 0u);
     r.st(MR_SP, 0u);
     r.st(MR_INST, TRAV_NONE);
     r.st(MR_FL, (tr.oi << 16) | (tr.oi << 19) | (any ? MR_FL_ANY : 0u));
-    r.st(MR_TRI, 0u); r.st(MR_TEND, 0u);
-    r.stf(MR_HUD, 0.0f); r.stf(MR_HVD, 0.0f); r.stf(MR_HDET, 1.0f);
-    r.st(MR_HSLOT, 0u);
+    if (!keep_hit)
+    {
+        r.stf(MR_HUD, 0.0f); r.stf(MR_HVD, 0.0f); r.stf(MR_HDET, 1.0f);
+        r.st(MR_HSLOT, 0u);
+    }
     r.st(MR_HINST, TRAV_NONE);
     return MT_N;
 }
@@ -103,8 +106,9 @@ template <class R> PTB_HD float mr_hit_u(const R& r) { return ex::div(r.ldf(MR_H
 template <class R> PTB_HD float mr_hit_v(const R& r) { return ex::div(r.ldf(MR_HVD), r.ldf(MR_HDET)); }
 
 // ---- P: next node from the current group, or pop (wide_step_pop without the instance entry) ------------------------------------
-template <class R>
-PTB_HD uint32_t mr_stage_p(const R& r, uint2* stk)
+// Job::world_ray(r, &o, &d): the ray's world-space origin and direction as they were given to mr_begin (re-read from the job's source)
+template <class R, class Job>
+PTB_HD uint32_t mr_stage_p(const R& r, uint2* stk, const Job& job)
 {
     uint32_t gx = r.ld(MR_GX), gy = r.ld(MR_GY);
     const uint32_t spw = r.ld(MR_SP);
@@ -118,7 +122,9 @@ PTB_HD uint32_t mr_stage_p(const R& r, uint2* stk)
             fl = (fl & ~(MR_FL_BLAS | (7u << 16))) | (((fl >> 19) & 7u) << 16);
             r.st(MR_FL, fl);
             r.st(MR_INST, TRAV_NONE);
-            r.st3(MR_O, r.ld3(MR_WO)); r.st3(MR_D, r.ld3(MR_WD)); r.st3(MR_INV, r.ld3(MR_INVW));
+            V3 o, d;
+            job.world_ray(r, &o, &d);
+            r.st3(MR_O, o); r.st3(MR_D, d); r.st3(MR_INV, r.ld3(MR_INVW));
         }
         if (sp == 0u) return MT_DONE;
         const uint2 e = stk[--sp];
@@ -222,84 +228,62 @@ PTB_HD uint32_t mr_stage_n(const R& r, const SceneDev& S, uint2* stk)
     return MT_P;
 }
 
-// ---- L + T: one reference leaf (exact box, exact t_enter) and / or one triangle --------------------------------------------------
-// tag L: the next hit leaf of the current node, and its first triangle when the box is hit; tag T: the next triangle of the open leaf.
+// ---- L: one reference leaf of the current BLAS node: exact box, exact t_enter, its triangles (reference leaves hold one or two) ------
 template <int MODE, class R>
-PTB_HD uint32_t mr_stage_lt(const R& r, const SceneDev& S, uint32_t tag)
+PTB_HD uint32_t mr_stage_l(const R& r, const SceneDev& S)
 {
     uint32_t fl = r.ld(MR_FL);
     const bool ANY = MODE == 2 ? ((fl & MR_FL_ANY) != 0u) : (MODE == 1);
     const V3 o = r.ld3(MR_O);
-    const float t_max = r.ldf(MR_TMAX);
-    float4 pa = {0.0f, 0.0f, 0.0f, 0.0f}, pb = pa, pc = pa;
-    uint32_t tri_i = 0u, tri_end = 0u;
+    float t_max = r.ldf(MR_TMAX);
+    const uint32_t lh0 = fl & 0xffu, lmask = (fl >> 8) & 0xffu;
+    const int p = hi_bit(lh0);
+    fl &= ~(1u << p);
+    r.st(MR_FL, fl);
+    const uint32_t sl = (uint32_t)p ^ ((fl >> 16) & 7u);
+    const uint32_t hidx = r.ld(MR_NODE) + popc32(lmask & ((1u << sl) - 1u));
+    const float4* lp = S.leaf_headers + (size_t)hidx * LEAF_F4;
+    const float4 h0 = PTB_LDG4F(lp), h1 = PTB_LDG4F(lp + 1);
+    float4 a = PTB_LDG4F(lp + 2), b = PTB_LDG4F(lp + 3), c = PTB_LDG4F(lp + 4);  // planes of the leaf's first triangle, fetched with its header
+    const uint32_t cw = ex::bits(h0.w);
     float t_enter = 0.0f;
-    bool have = false, fresh = false;
-    if (tag == MT_L)
+    bool go = true;
+    PTB_STAT(1);
+    // blas.rs:137-138 / :264 — exact reference leaf box, exact entry distance (the BLAS root is entered untested with t_estimate = 0 by
+    // the closest-hit query, blas.rs:217)
+    if (ANY || !(cw & LEAF_ROOT_FLAG)) go = ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), o, r.ld3(MR_INV), t_max, &t_enter);
+    if (go)
     {
-        const uint32_t lh0 = fl & 0xffu, lmask = (fl >> 8) & 0xffu;
-        const int p = hi_bit(lh0);
-        fl &= ~(1u << p);
-        r.st(MR_FL, fl);
-        const uint32_t sl = (uint32_t)p ^ ((fl >> 16) & 7u);
-        const uint32_t hidx = r.ld(MR_NODE) + popc32(lmask & ((1u << sl) - 1u));
-        const float4* lp = S.leaf_headers + (size_t)hidx * LEAF_F4;
-        const float4 h0 = PTB_LDG4F(lp), h1 = PTB_LDG4F(lp + 1);
-        pa = PTB_LDG4F(lp + 2); pb = PTB_LDG4F(lp + 3); pc = PTB_LDG4F(lp + 4);
-        const uint32_t cw = ex::bits(h0.w);
-        bool go = true;
-        PTB_STAT(1);
-        if (ANY || !(cw & LEAF_ROOT_FLAG)) go = ex::slab(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), o, r.ld3(MR_INV), t_max, &t_enter);
-        if (go)
+        const V3 d = r.ld3(MR_D);
+        uint32_t tri_i = ex::bits(h1.w);
+        const uint32_t tri_end = tri_i + (cw & ~LEAF_ROOT_FLAG);
+        for (;;)
         {
-            tri_i = ex::bits(h1.w);
-            tri_end = tri_i + (cw & ~LEAF_ROOT_FLAG);
-            have = fresh = true;
-        }
-    }
-    else
-    {
-        tri_i = r.ld(MR_TRI);
-        tri_end = r.ld(MR_TEND);
-        t_enter = r.ldf(MR_TENTER);
-        have = true;
-    }
-    if (have)
-    {
-        PTB_STAT(2);
-        float4 a = pa, b = pb, c = pc;
-        if (!fresh)
-        {
+            PTB_STAT(2);
+            const float n0[4] = {a.x, a.y, a.z, a.w}, n1[4] = {b.x, b.y, b.z, b.w}, n2[4] = {c.x, c.y, c.z, c.w};
+            if (ANY)
+            {
+                if (ex::tri_hit_bool(n0, n1, n2, o, d, t_max, t_enter))
+                {
+                    r.st(MR_HINST, r.ld(MR_INST));
+                    return MT_DONE;
+                }
+            }
+            else
+            {
+                float t, raw[3];
+                if (ex::tri_hit_raw(n0, n1, n2, o, d, t_max, t_enter, &t, raw))
+                {
+                    t_max = t;
+                    r.stf(MR_TMAX, t);
+                    r.stf(MR_HUD, raw[0]); r.stf(MR_HVD, raw[1]); r.stf(MR_HDET, raw[2]);
+                    r.st(MR_HSLOT, tri_i);
+                    r.st(MR_HINST, r.ld(MR_INST));
+                }
+            }
+            if (++tri_i >= tri_end) break;
             const float4* pp = S.tri_planes + (size_t)tri_i * 3;
             a = PTB_LDG4F(pp); b = PTB_LDG4F(pp + 1); c = PTB_LDG4F(pp + 2);
-        }
-        const V3 d = r.ld3(MR_D);
-        const float n0[4] = {a.x, a.y, a.z, a.w}, n1[4] = {b.x, b.y, b.z, b.w}, n2[4] = {c.x, c.y, c.z, c.w};
-        if (ANY)
-        {
-            if (ex::tri_hit_bool(n0, n1, n2, o, d, t_max, t_enter))
-            {
-                r.st(MR_HINST, r.ld(MR_INST));
-                return MT_DONE;
-            }
-        }
-        else
-        {
-            float t, raw[3];
-            if (ex::tri_hit_raw(n0, n1, n2, o, d, t_max, t_enter, &t, raw))
-            {
-                r.stf(MR_TMAX, t);
-                r.stf(MR_HUD, raw[0]); r.stf(MR_HVD, raw[1]); r.stf(MR_HDET, raw[2]);
-                r.st(MR_HSLOT, tri_i);
-                r.st(MR_HINST, r.ld(MR_INST));
-            }
-        }
-        ++tri_i;
-        if (tri_i < tri_end)
-        {
-            r.st(MR_TRI, tri_i);
-            if (fresh) { r.st(MR_TEND, tri_end); r.stf(MR_TENTER, t_enter); }
-            return MT_T;
         }
     }
     return (fl & 0xffu) ? MT_L : MT_P;
@@ -312,8 +296,9 @@ PTB_HD uint32_t mr_stage_lt(const R& r, const SceneDev& S, uint32_t tag)
 //   uint32_t start(uint32_t index, const R& r)        fetch work item `index`; returns the ray's first tag (mr_begin) or MT_IDLE
 //   uint32_t finish(const R& r, bool mine)            called by ALL lanes of the warp together; `mine` = r is a finished ray of this lane.
 //                                                     Returns the tag of a follow-up traversal (mr_begin) or MT_IDLE.
+//   void world_ray(const R& r, V3* o, V3* d)          the world-space ray given to mr_begin, re-read from the job's source
 // free_quorum: finished / idle ray slots of the warp that trigger a finish + start pass; qn / ql / qi: lanes that must hold a ray
-// waiting for the node / leaf-triangle / instance stage before the warp runs it (all stages run when none reaches its quorum).
+// waiting for the node / leaf / instance stage before the warp runs it (all stages run when none reaches its quorum).
 template <int MODE, int K, class Job>
 __device__ __forceinline__ void mr_persistent_trace(const SceneDev& S, Job& job, uint32_t* cursor, uint32_t total, int free_quorum, int qn, int ql, int qi)
 {
@@ -333,20 +318,21 @@ __device__ __forceinline__ void mr_persistent_trace(const SceneDev& S, Job& job,
     const uint32_t fair = max(1u, (total + n_warps * K - 1u) / (n_warps * K));
     uint32_t wbase = 0, wend = 0, seen = 0;
     bool global_more = total > 0u;
+    int n_free = 32 * K, n_done = 0;  // warp-uniform: ray slots that are idle or finished, and the finished ones among them
     for (;;)
     {
         // ---- finish + start --------------------------------------------------------------------------------------------------------
-        const int n_done = (int)__reduce_add_sync(FULL, (unsigned)mr_count2<K>(tags, MT_DONE, MT_DONE));
-        const int n_idle = (int)__reduce_add_sync(FULL, (unsigned)mr_count2<K>(tags, MT_IDLE, MT_IDLE));
-        const int n_act = 32 * K - n_done - n_idle;
         bool more = wbase < wend || global_more;
-        if (more ? (n_done + n_idle >= free_quorum) : (n_done > 0 && (n_done >= 8 || n_act == 0)))
+        if (more ? (n_free >= free_quorum) : (n_done > 0 && (n_done >= 8 || n_free == 32 * K)))
         {
             if (n_done)
             {
                 const int k = mr_first<K>(tags, MT_DONE);
                 const uint32_t t = job.finish(ray(k < 0 ? 0 : k), k >= 0);
                 if (k >= 0) tags = mr_set(tags, k, t);
+                const int again = __popc(__ballot_sync(FULL, k >= 0 && t != MT_IDLE)), fin = __popc(__ballot_sync(FULL, k >= 0));
+                n_done -= fin;
+                n_free -= again;
             }
             for (int pass = 0; pass < K && (wbase < wend || global_more); ++pass)
             {
@@ -365,24 +351,32 @@ __device__ __forceinline__ void mr_persistent_trace(const SceneDev& S, Job& job,
                 }
                 const uint32_t avail = wend - wbase, n = (uint32_t)__popc(idle);
                 const uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
-                if (k >= 0 && rank < avail) tags = mr_set(tags, k, job.start(wbase + rank, ray(k)));
+                uint32_t t = MT_IDLE;
+                if (k >= 0 && rank < avail) tags = mr_set(tags, k, t = job.start(wbase + rank, ray(k)));
+                n_free -= __popc(__ballot_sync(FULL, t != MT_IDLE));
                 wbase += min(n, avail);
             }
             more = wbase < wend || global_more;
         }
-        if (!__any_sync(FULL, tags != 0u))
+        if (n_free == 32 * K)
         {
-            if (!more) break;
+            if (!more && n_done == 0) break;
             continue;
         }
         // ---- P ---------------------------------------------------------------------------------------------------------------------
+        unsigned fin = 0u;
         {
             const int k = mr_first<K>(tags, MT_P);
-            if (k >= 0) tags = mr_set(tags, k, mr_stage_p(ray(k), lstack[k]));
+            if (k >= 0)
+            {
+                const uint32_t t = mr_stage_p(ray(k), lstack[k], job);
+                tags = mr_set(tags, k, t);
+                fin = t == MT_DONE ? 1u : 0u;
+            }
         }
         // ---- which stages run ------------------------------------------------------------------------------------------------------
         const int cn = __popc(__ballot_sync(FULL, mr_has<K>(tags, MT_N)));
-        const int cl = __popc(__ballot_sync(FULL, mr_has2<K>(tags, MT_L, MT_T)));
+        const int cl = __popc(__ballot_sync(FULL, mr_has<K>(tags, MT_L)));
         const int ci = __popc(__ballot_sync(FULL, mr_has<K>(tags, MT_I)));
         bool run_n = cn >= qn, run_l = cl >= ql, run_i = ci >= qi;
         if (!(run_n && cn) && !(run_l && cl) && !(run_i && ci)) run_n = run_l = run_i = true;
@@ -391,18 +385,24 @@ __device__ __forceinline__ void mr_persistent_trace(const SceneDev& S, Job& job,
             const int k = mr_first<K>(tags, MT_I);
             if (k >= 0) tags = mr_set(tags, k, mr_stage_i(ray(k), S));
         }
-        if (run_n)
+        if (run_n && cn)
         {
             const int k = mr_first<K>(tags, MT_N);
             if (k >= 0) tags = mr_set(tags, k, mr_stage_n(ray(k), S, lstack[k]));
         }
         if (run_l)
         {
-            int k = mr_first<K>(tags, MT_L);
-            uint32_t tag = MT_L;
-            if (k < 0) { k = mr_first<K>(tags, MT_T); tag = MT_T; }
-            if (k >= 0) tags = mr_set(tags, k, mr_stage_lt<MODE>(ray(k), S, tag));
+            const int k = mr_first<K>(tags, MT_L);
+            if (k >= 0)
+            {
+                const uint32_t t = mr_stage_l<MODE>(ray(k), S);
+                tags = mr_set(tags, k, t);
+                fin += t == MT_DONE ? 1u : 0u;
+            }
         }
+        const int f = (int)__reduce_add_sync(FULL, fin);
+        n_done += f;
+        n_free += f;
     }
 }
 #endif

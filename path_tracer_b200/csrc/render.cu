@@ -20,6 +20,7 @@
 
 #include "camera_host.h"
 #include "context.h"
+#include "multiray.cuh"
 #include "persist.cuh"
 #include "render_state.h"
 #include "wavefront.h"
@@ -426,6 +427,209 @@ __global__ void __launch_bounds__(128, MB) k_nee(RenderView V, Queues Q, uint32_
     WfSet& S = Q.c->set[it % 3u];
     NeeJob job{V, Q};
     persistent_trace<2, NeeJob, false, SSTACK>(V.S, job, &S.cur_nee, S.n_nee, refill_below, node_quorum);
+    const unsigned long long a = warp_sum(job.n_shadow), b = warp_sum(job.n_probe), c = warp_sum(job.n_probe_shadow);
+    if ((threadIdx.x & 31u) == 0u)
+    {
+        if (a) atomicAdd(&Q.c->stat_shadow, a);
+        if (b) atomicAdd(&Q.c->stat_probe, b);
+        if (c) atomicAdd(&Q.c->stat_probe_shadow, c);
+    }
+}
+
+// ---- the same two kernels with K rays per lane and gated stages (multiray.cuh; option `multiray` = K) ------------------------------
+// Jobs as above with their per-ray data in the ray record's job words; per-ray arithmetic and its order are unchanged, so frames are
+// bit-identical to the one-ray-per-lane kernels'.
+struct MrExtendJob
+{
+    static constexpr int JOBW = 1;  // [0] slot
+    const RenderView& V;
+    const Queues& Q;
+    WfSet& S;
+    uint32_t b, n_cont, n_term;
+    int sort;
+    unsigned long long paths = 0, settled = 0;
+
+    template <class R>
+    __device__ __forceinline__ uint32_t start(uint32_t idx, const R& r)
+    {
+        V3 o, d;
+        uint32_t slot;
+        if (idx < n_cont)
+        {
+            slot = Q.cont[b][idx];
+            const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
+            o = ex::v3(o4.x, o4.y, o4.z);
+            d = ex::v3(d4.x, d4.y, d4.z);
+        }
+        else
+        {
+            slot = Q.term[b][idx - n_cont];
+            for (;;)
+            {
+                const uint32_t f = regen_slot(V, slot, &o, &d) & WF_NEXT;
+                if (!f) { Q.state[slot] = 0u; return MT_IDLE; }  // out of samples
+                ++paths;
+                if (sort >= 0 || V.S.env != nullptr || tlas_may_hit(V.S, 0, o, d)) break;  // see ExtendJob::start
+                V.path[slot].radiance = f4(0.006f, 0.006f, 0.006f, 0.0f);
+                ++settled;
+            }
+            Q.state[slot] = WF_NEXT;
+        }
+        r.st(MR_JOB, slot);
+        return mr_begin(r, V.S, 0, o, d, ex::inf(), false);
+    }
+    template <class R>
+    __device__ __forceinline__ void world_ray(const R& r, V3* o, V3* d) const
+    {
+        const uint32_t slot = r.ld(MR_JOB);
+        const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
+        *o = ex::v3(o4.x, o4.y, o4.z);
+        *d = ex::v3(d4.x, d4.y, d4.z);
+    }
+    template <class R>
+    __device__ __forceinline__ uint32_t finish(const R& r, bool mine)
+    {
+        uint32_t kind = 0xffu, slot = 0u;
+        if (mine)
+        {
+            slot = r.ld(MR_JOB);
+            const uint32_t hit_inst = r.ld(MR_HINST);
+            if (hit_inst == TRAV_NONE)
+            {
+                V.hit[slot].info = 0xffffffffu;
+                V.hit[slot].kind = kind = Q_MISS;
+            }
+            else
+            {
+                const uint32_t prim = V.S.tri_prim[r.ld(MR_HSLOT)];
+                V3 n;
+                bool ff;
+                finish_hit(V.S, r.ld3(MR_D), hit_inst, prim, mr_hit_u(r), mr_hit_v(r), &n, &ff);  // a finished closest-hit ray is back in world space
+                V.hit[slot].tn = f4(r.ldf(MR_TMAX), n.x, n.y, n.z);
+                V.hit[slot].info = hit_inst | (ff ? 0x80000000u : 0u);
+                V.hit[slot].kind = kind = V.S.mat[V.S.inst[hit_inst].blas].kind;
+            }
+            if (sort == 0) kind = 0u;
+        }
+        if (sort >= 0) warp_push_keyed(Q.mat, Q.npix, S.n_mat, kind, slot);
+        return MT_IDLE;
+    }
+};
+
+template <int K>
+__global__ void __launch_bounds__(128) k_extend_mr(RenderView V, Queues Q, uint32_t it, int sort, MrOpts mo)
+{
+    WfSet& S = Q.c->set[it % 3u];
+    const uint32_t n_cont = S.n_cont, n_term = S.n_term;
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+    {
+        Q.c->set[(it + 2u) % 3u] = WfSet{};
+        if (n_cont + n_term) Q.c->stat_iters += 1;
+    }
+    MrExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort};
+    mr_persistent_trace<0, K>(V.S, job, &S.cur_extend, n_cont + n_term, mo.free_quorum, mo.qn, mo.ql, mo.qi);
+    const unsigned long long p = warp_sum(job.paths), q = warp_sum(job.settled);
+    if ((threadIdx.x & 31u) == 0u && p) atomicAdd(&Q.c->stat_paths, p);
+    if ((threadIdx.x & 31u) == 0u && q) atomicAdd(&Q.c->stat_settled, q);
+}
+
+struct MrNeeJob
+{
+    static constexpr int JOBW = 4;  // [0] nee queue entry (slot | flags), [1] stage, [2] t of the light hit (stage 1), [3] its instance
+    const RenderView& V;
+    const Queues& Q;
+    unsigned long long n_shadow = 0, n_probe = 0, n_probe_shadow = 0;
+
+    template <class R>
+    __device__ __forceinline__ V3 origin(const R& r) const
+    {
+        const float4 o4 = V.ray[r.ld(MR_JOB) & NEE_SLOT_MASK].o;
+        return ex::v3(o4.x, o4.y, o4.z);
+    }
+    template <class R>
+    __device__ __forceinline__ void world_ray(const R& r, V3* o, V3* d) const
+    {
+        const uint32_t slot = r.ld(MR_JOB) & NEE_SLOT_MASK;
+        *o = origin(r);
+        const float4 d4 = r.ld(MR_JOB + 1) == 0u ? V.shadow[slot].d : V.probe[slot].d;
+        *d = ex::v3(d4.x, d4.y, d4.z);
+    }
+    template <class R>
+    __device__ __forceinline__ uint32_t begin_probe(const R& r, uint32_t slot, V3 o)
+    {
+        const float4 d4 = V.probe[slot].d;
+        const V3 d = ex::v3(d4.x, d4.y, d4.z);
+        ++n_probe;
+        if (!tlas_may_hit(V.S, 1, o, d)) return MT_IDLE;
+        r.st(MR_JOB + 1, 1u);
+        return mr_begin(r, V.S, 1, o, d, ex::inf(), false);
+    }
+    template <class R>
+    __device__ __forceinline__ uint32_t start(uint32_t idx, const R& r)
+    {
+        const uint32_t e = Q.nee[idx], slot = e & NEE_SLOT_MASK;
+        r.st(MR_JOB, e);
+        const float4 o4 = V.ray[slot].o;
+        const V3 o = ex::v3(o4.x, o4.y, o4.z);
+        if (e & NEE_SHADOW_BIT)
+        {
+            const float4 d4 = V.shadow[slot].d;
+            r.st(MR_JOB + 1, 0u);
+            ++n_shadow;
+            return mr_begin(r, V.S, 0, o, ex::v3(d4.x, d4.y, d4.z), d4.w, true);
+        }
+        return begin_probe(r, slot, o);
+    }
+    // the two estimates of a bounce are added to the radiance one after the other (nee_slot_t's order): two read-modify-writes here
+    __device__ __forceinline__ void add_radiance(uint32_t slot, float x, float y, float z)
+    {
+        float4 rr = V.path[slot].radiance;
+        rr.x += x; rr.y += y; rr.z += z;
+        V.path[slot].radiance = rr;
+    }
+    template <class R>
+    __device__ __forceinline__ uint32_t finish(const R& r, bool mine)
+    {
+        if (!mine) return MT_IDLE;
+        const uint32_t e = r.ld(MR_JOB), slot = e & NEE_SLOT_MASK, stage = r.ld(MR_JOB + 1);
+        const bool hit = r.ld(MR_HINST) != TRAV_NONE;
+        if (stage == 0u)
+        {
+            if (!hit)
+            {
+                const float4 c = V.shadow[slot].c;
+                add_radiance(slot, c.x, c.y, c.z);
+            }
+            if (e & NEE_PROBE_BIT) return begin_probe(r, slot, origin(r));
+        }
+        else if (stage == 1u)
+        {
+            if (hit)
+            {
+                const float lt = r.ldf(MR_TMAX);
+                r.stf(MR_JOB + 2, lt);
+                r.st(MR_JOB + 3, r.ld(MR_HINST));
+                r.st(MR_JOB + 1, 2u);
+                ++n_probe_shadow;
+                return mr_begin(r, V.S, 0, origin(r), r.ld3(MR_D), lt * (1.0f - ex::EPS), true, true);  // MR_D: the probe direction, back in world space
+            }
+        }
+        else if (!hit)
+        {
+            const float4 d4 = V.probe[slot].d;
+            const V3 c = probe_light_contrib(V, slot, ex::v3(d4.x, d4.y, d4.z), r.ldf(MR_JOB + 2), mr_hit_u(r), mr_hit_v(r), V.S.tri_prim[r.ld(MR_HSLOT)], r.ld(MR_JOB + 3));
+            add_radiance(slot, c.x, c.y, c.z);
+        }
+        return MT_IDLE;
+    }
+};
+
+template <int K>
+__global__ void __launch_bounds__(128) k_nee_mr(RenderView V, Queues Q, uint32_t it, MrOpts mo)
+{
+    WfSet& S = Q.c->set[it % 3u];
+    MrNeeJob job{V, Q};
+    mr_persistent_trace<2, K>(V.S, job, &S.cur_nee, S.n_nee, mo.free_quorum, mo.qn, mo.ql, mo.qi);
     const unsigned long long a = warp_sum(job.n_shadow), b = warp_sum(job.n_probe), c = warp_sum(job.n_probe_shadow);
     if ((threadIdx.x & 31u) == 0u)
     {
@@ -1333,6 +1537,39 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     }
     for (int g = 0; g < G; ++g) gr[g].dense = !bin && ctx->opt_dense != 0;
 
+    // multiray kernels (option multiray = 2 / 3 rays per lane, multiray.cuh): dynamic shared memory for the ray records, as many resident
+    // blocks per SM as fit (or mr_blocks)
+    // automatic (-1): two rays per lane when the scene's trees are large enough for the stages of a warp to diverge and for a ray to live
+    // long enough to repay its record set-up (measured: C3, 519 wide nodes, + 6.4 % per frame, C4, 1.03 M nodes, + 5.5 %; C1, 332 nodes, - 3 %,
+    // C2, 8 nodes, - 3.5 % — the threshold sits between those, the option overrides it)
+    const int mr_want = ctx->opt_multiray < 0 ? (ctx->scene.wide.size() >= 384 ? 2 : 0) : ctx->opt_multiray;
+    const int mr_k = (!bin && threads == 128 && (mr_want == 2 || mr_want == 3)) ? mr_want : 0;
+    MrOpts mro = ctx->opt_mr;
+    if (mro.free_quorum <= 0) mro.free_quorum = 24;
+    const size_t mr_es = (size_t)mr_k * (MR_JOB + MrExtendJob::JOBW) * 128 * sizeof(uint32_t), mr_ns = (size_t)mr_k * (MR_JOB + MrNeeJob::JOBW) * 128 * sizeof(uint32_t);
+    int mr_eb = 0, mr_nb = 0;
+    // thin iterations (fewer live slots than mr_min_per_lane per resident lane of the one-ray kernels) go to the one-ray-per-lane kernels:
+    // a lane that holds one ray only waits at every gate
+    const uint32_t mr_min = (uint32_t)std::max(0, ctx->opt_mr_min_per_lane) * (uint32_t)(ctx->sm_count * 7 * 128);
+    if (mr_k)
+    {
+        if (mr_k == 3)
+        {
+            PTB_CUDA(ctx, cudaFuncSetAttribute(k_extend_mr<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mr_es));
+            PTB_CUDA(ctx, cudaFuncSetAttribute(k_nee_mr<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mr_ns));
+            PTB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&mr_eb, k_extend_mr<3>, 128, mr_es));
+            PTB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&mr_nb, k_nee_mr<3>, 128, mr_ns));
+        }
+        else
+        {
+            PTB_CUDA(ctx, cudaFuncSetAttribute(k_extend_mr<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mr_es));
+            PTB_CUDA(ctx, cudaFuncSetAttribute(k_nee_mr<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mr_ns));
+            PTB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&mr_eb, k_extend_mr<2>, 128, mr_es));
+            PTB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&mr_nb, k_nee_mr<2>, 128, mr_ns));
+        }
+        if (mro.blocks_per_sm > 0) { mr_eb = std::min(mr_eb, mro.blocks_per_sm); mr_nb = std::min(mr_nb, mro.blocks_per_sm); }
+        if (mr_eb < 1 || mr_nb < 1) return ctx->fail(PTB_ERR_CUDA, "multiray kernels do not fit on this device");
+    }
     // Grid of a persistent traversal / queue kernel compiled for `blocks` resident blocks per SM, given an upper bound of the work items.
     // shared_device = 1 (two contexts rendering alternate frames on one device, ptb_render_async): the dense launches leave one block
     // slot per SM free and the thin ones take only the blocks their work fills at thin_rays_per_lane items per lane, so the other
@@ -1372,6 +1609,13 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         const bool dense = R.dense;
         const int rb = ctx->opt_refill_below, rbn = ctx->opt_nee_refill_below, nq = ctx->opt_node_quorum;
         if (bin) k_extend_bin<<<grid, threads, 0, gs>>>(V, Q, it);
+        else if (mr_k && R.bound >= mr_min)
+        {
+            const int so = dense ? -1 : (sort ? 1 : 0);
+            const int eg = sized_grid(mr_eb, R.bound);
+            if (mr_k == 3) k_extend_mr<3><<<eg, 128, mr_es, gs>>>(V, Q, it, so, mro);
+            else k_extend_mr<2><<<eg, 128, mr_es, gs>>>(V, Q, it, so, mro);
+        }
         else
         {
             const int so = dense ? -1 : (sort ? 1 : 0);
@@ -1399,6 +1643,12 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         if (V.enable_nee)
         {
             if (bin) k_nee_bin<<<grid, threads, 0, gs>>>(V, Q, it);
+            else if (mr_k && R.bound >= mr_min)
+            {
+                const int ng = sized_grid(mr_nb, R.bound);
+                if (mr_k == 3) k_nee_mr<3><<<ng, 128, mr_ns, gs>>>(V, Q, it, mro);
+                else k_nee_mr<2><<<ng, 128, mr_ns, gs>>>(V, Q, it, mro);
+            }
             else
             {
                 const int nb = (ctx->opt_nee_blocks == 4 || ctx->opt_nee_blocks == 6 || ctx->opt_nee_blocks == 7 || ctx->opt_nee_blocks == 8) ? ctx->opt_nee_blocks : 5;

@@ -226,6 +226,16 @@ static void emu_mr_warp(const SceneDev& S, int which, int any, uint64_t n, const
     auto ray = [&](int lane, int k) { return R{mem.data() + ((size_t)lane * K + k) * NW}; };
     auto stack = [&](int lane, int k) { return stk.data() + ((size_t)lane * K + k) * WIDE_STACK_CAP; };
     uint64_t next = 0;
+    struct WorldRay
+    {
+        const float *o, *d;
+        void world_ray(const R& r, V3* oo, V3* dd) const
+        {
+            const uint64_t i = r.ld(MR_JOB);
+            *oo = ex::v3(o[i * 3], o[i * 3 + 1], o[i * 3 + 2]);
+            *dd = ex::v3(d[i * 3], d[i * 3 + 1], d[i * 3 + 2]);
+        }
+    } job{o, d};
     for (;;)
     {
         int n_done = 0, n_idle = 0;
@@ -270,10 +280,10 @@ static void emu_mr_warp(const SceneDev& S, int which, int any, uint64_t n, const
         for (int l = 0; l < 32; ++l)
         {
             const int k = mr_first<K>(tags[l], MT_P);
-            if (k >= 0) tags[l] = mr_set(tags[l], k, mr_stage_p(ray(l, k), stack(l, k)));
+            if (k >= 0) tags[l] = mr_set(tags[l], k, mr_stage_p(ray(l, k), stack(l, k), job));
         }
         int cn = 0, cl = 0, ci = 0;
-        for (int l = 0; l < 32; ++l) { cn += mr_has<K>(tags[l], MT_N); cl += mr_has2<K>(tags[l], MT_L, MT_T); ci += mr_has<K>(tags[l], MT_I); }
+        for (int l = 0; l < 32; ++l) { cn += mr_has<K>(tags[l], MT_N); cl += mr_has<K>(tags[l], MT_L); ci += mr_has<K>(tags[l], MT_I); }
         bool run_n = cn >= qn, run_l = cl >= ql, run_i = ci >= qi;
         if (!(run_n && cn) && !(run_l && cl) && !(run_i && ci)) run_n = run_l = run_i = true;
         if (stats) { stats[1] += run_n && cn; stats[2] += run_n ? cn : 0; stats[3] += run_l && cl; stats[4] += run_l ? cl : 0; stats[5] += run_i && ci; stats[6] += run_i ? ci : 0; }
@@ -291,10 +301,8 @@ static void emu_mr_warp(const SceneDev& S, int which, int any, uint64_t n, const
             }
             if (run_l)
             {
-                int k = mr_first<K>(tags[l], MT_L);
-                uint32_t tag = MT_L;
-                if (k < 0) { k = mr_first<K>(tags[l], MT_T); tag = MT_T; }
-                if (k >= 0) tags[l] = mr_set(tags[l], k, mr_stage_lt<2>(ray(l, k), S, tag));
+                const int k = mr_first<K>(tags[l], MT_L);
+                if (k >= 0) tags[l] = mr_set(tags[l], k, mr_stage_l<2>(ray(l, k), S));
             }
         }
     }

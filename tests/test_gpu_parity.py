@@ -361,6 +361,55 @@ def test_path_kernel_equals_wavefront(ptb, scenes, name, spp, W, H):
         assert np.allclose(ref[0], v[0], rtol=1e-5, atol=1e-7), f"{k}: radiance differs beyond rounding"
 
 
+@pytest.mark.parametrize("name", ["c2", "c3_small", "materials", "c4_small"])
+def test_multiray_trace_equals_lane(ptb, scenes, name):
+    """Multiray traversal (multiray.cuh: K = 1 ... 4 rays per lane, gated stages, ray records in shared memory; ptb_trace_* kernel 6 / 3 / 4 / 5)
+    against the one-ray-per-lane persistent kernel: the per-ray arithmetic and visit order are the same, so every output is bit-identical
+    — hit, t, u, v, prim, instance, normal — for both TLASes, closest and any hit, at several quorum settings."""
+    sd = _scene(scenes, name)
+    ctx = ptb.Context(0)
+    ctx.upload(sd)
+    n = 1 << 16
+    o, d, tm = scenes.incoherent_rays(sd, n, seed=5)
+    inf = np.full(n, np.inf, np.float32)
+    for which in (0, 1):
+        ref = ctx.trace_closest(o, d, inf, which=which, kernel=0)
+        refa = ctx.trace_any(o, d, tm, which=which, kernel=0)
+        for kernel, (fq, qn, ql, qi) in ((6, (24, 8, 1, 1)), (3, (24, 16, 12, 12)), (3, (8, 1, 1, 1)), (4, (40, 20, 16, 8)), (5, (24, 16, 8, 12))):
+            for k, v in (("mr_free_quorum", fq), ("mr_qn", qn), ("mr_ql", ql), ("mr_qi", qi)):
+                ctx.set_option(k, v)
+            g = ctx.trace_closest(o, d, inf, which=which, kernel=kernel)
+            for key in ("hit", "prim", "inst", "blas", "front"):
+                assert np.array_equal(g[key], ref[key]), f"{name} which={which} kernel={kernel}: {key} differs"
+            for key in ("t", "u", "v", "normal"):
+                assert np.array_equal(bits(g[key]), bits(ref[key])), f"{name} which={which} kernel={kernel}: {key} differs"
+            assert np.array_equal(ctx.trace_any(o, d, tm, which=which, kernel=kernel)["hit"], refa["hit"]), f"{name} which={which} kernel={kernel}: any-hit differs"
+
+
+@pytest.mark.parametrize("name,spp,W,H", [("c2", 6, 96, 54), ("c3_small", 5, 97, 53), ("materials", 19, 33, 21), ("c1", 4, 64, 36)])
+def test_multiray_render_equals_lane(ptb, scenes, name, spp, W, H):
+    """k_extend_mr / k_nee_mr (option multiray = 2, 3) against k_extend / k_nee: same per-slot bodies, same per-ray traversal results, the
+    two NEE estimates added to the radiance in the same order — the frame, the aux outputs and the ray counters are bit-identical."""
+    sd = _scene(scenes, name)
+    out = {}
+    for mr, fq in ((0, 24), (2, 24), (3, 24), (2, 8)):
+        ctx = ptb.Context(0)
+        ctx.upload(sd)
+        ctx.set_option("multiray", mr)
+        ctx.set_option("mr_free_quorum", fq)
+        ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
+        ctx.frame_begin(W, H)
+        ctx.reset_counters()
+        ctx.render(0, spp, seed=29, max_bounces=sd.max_bounces)
+        pos, ids = ctx.read_aux()
+        c = ctx.counters()
+        out[(mr, fq)] = (bits(ctx.read_accum()), bits(pos), ids.copy(), (c["extend"], c["settled"], c["shadow"], c["probe"], c["paths"]))
+    ref = out[(0, 24)]
+    for k, v in out.items():
+        assert ref[3] == v[3], f"multiray={k}: ray counters differ: {ref[3]} vs {v[3]}"
+        assert all(np.array_equal(a, b) for a, b in zip(ref[:3], v[:3])), f"multiray={k}: outputs differ"
+
+
 def _group_render(group, sd, W, H, begin, count, seed):
     group.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
     group.frame_begin(W, H)

@@ -84,9 +84,11 @@ for label, o, d, tm in batches():
     if quick:
         continue
     # quorum / occupancy sweeps, closest hit
-    for k in (3, 4, 5):
-        for (fq, qn, ql, qi, bl) in ((24, 16, 12, 12, 0), (24, 16, 8, 8, 0), (24, 8, 1, 1, 0), (24, 20, 16, 16, 0), (24, 12, 8, 8, 0), (16, 16, 12, 12, 0), (40, 16, 12, 12, 0),
-                                     (24, 16, 12, 12, 2), (24, 16, 12, 12, 3), (24, 16, 12, 12, 4), (24, 16, 12, 12, 5)):
+    for k in (6, 3, 4, 5):
+        for (fq, qn, ql, qi, bl) in ((24, 16, 12, 12, 0), (24, 16, 8, 8, 0), (24, 8, 1, 1, 0), (24, 20, 16, 16, 0), (16, 16, 12, 12, 0), (40, 16, 12, 12, 0),
+                                     (24, 16, 8, 8, 4), (24, 16, 8, 8, 5), (24, 16, 8, 8, 6), (24, 16, 8, 8, 7), (24, 16, 8, 8, 8)):
+            if k == 6 and fq == 40:
+                continue
             opts(fq, qn, ql, qi, bl)
             ctx.trace_resident(kernel=k, any_hit=False, repeats=1)
             ms = ctx.trace_resident(kernel=k, any_hit=False, repeats=4)
