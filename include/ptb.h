@@ -228,6 +228,8 @@ int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, floa
  *   dense             1 k_shade_ordered (slot-ordered shading, ascending queues; default), 0 the queue shade kernel throughout
  *   dense_threshold   live slots per listed 32-slot group, in percent, below which the queue shade kernel takes over (default 60)
  *   shade_sort        span-local sort by shade kind in k_shade_ordered: 1, 0, < 0 automatic (scenes with >= 2 surface material kinds)
+ *   shade_class       k_shade_ordered compiled for the scene's class of materials (< 0, default: Lambertian + Emissive / + GGX metal /
+ *                     all kinds, each without media; the kinds a scene does not hold are compiled out) or the general body (0)
  *   sort_materials    queue shade kernel: one queue per material kind (default 1)
  *   extend_blocks, nee_blocks   resident blocks per SM (= register cap) of k_extend (5..8, default 7) / k_nee (4..8, default 8)
  *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit 8, any-hit 8)

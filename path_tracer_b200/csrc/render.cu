@@ -32,7 +32,7 @@ struct WfSet  // 64 B
     uint32_t n_cont, n_term;  // consumed by k_extend (polled by the host: keep first)
     uint32_t n_nee, n_grp;    // n_grp: slot-ordered mode, live 32-slot groups listed for this iteration (polled with the two above)
     uint32_t n_mat[8];
-    uint32_t cur_extend, cur_shade, cur_nee, pad;
+    uint32_t cur_extend, cur_shade, cur_nee, cur_regen;  // cur_regen: cursor of the regeneration part when k_extend is launched in two parts
 };
 struct WfCounters
 {
@@ -188,10 +188,12 @@ struct ExtendJob
     int sort;  // 1: push the slot to the shade queue of its material kind, 0: to queue 0, -1: no push (k_shade_ordered walks the slots itself)
     uint32_t slot = 0;
     unsigned long long paths = 0, settled = 0;
+    uint32_t idx0 = 0;  // first work item of this launch (two-part launches: the regeneration part starts at n_cont)
 
     __device__ __forceinline__ bool start(uint32_t idx, WideTrav& tr)
     {
         V3 o, d;
+        idx += idx0;
         if (idx < n_cont)
         {
             slot = Q.cont[b][idx];
@@ -247,18 +249,21 @@ struct ExtendJob
     }
 };
 
+// part 0: the whole queue (continuing slots, then the slots to regenerate); part 2: the regeneration part only — the continuing slots
+// went to k_extend_mr (part 1) in a launch of their own: primary rays are coherent and run faster one per lane, bounce rays two per lane
 template <int MB, int SSTACK = 0>
-__global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint32_t it, int sort, int refill_below, int node_quorum)
+__global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint32_t it, int sort, int refill_below, int node_quorum, int part = 0)
 {
     WfSet& S = Q.c->set[it % 3u];
     const uint32_t n_cont = S.n_cont, n_term = S.n_term;
-    if (blockIdx.x == 0 && threadIdx.x == 0)
+    if (part == 0 && blockIdx.x == 0 && threadIdx.x == 0)
     {
         Q.c->set[(it + 2u) % 3u] = WfSet{};  // consumed in iteration it-1, refilled from iteration it+1 on
         if (n_cont + n_term) Q.c->stat_iters += 1;
     }
     ExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort};
-    persistent_trace<0, ExtendJob, false, SSTACK>(V.S, job, &S.cur_extend, n_cont + n_term, refill_below, node_quorum);
+    if (part == 2) job.idx0 = n_cont;
+    persistent_trace<0, ExtendJob, false, SSTACK>(V.S, job, part == 2 ? &S.cur_regen : &S.cur_extend, part == 2 ? n_term : n_cont + n_term, refill_below, node_quorum);
     const unsigned long long p = warp_sum(job.paths), q = warp_sum(job.settled);
     if ((threadIdx.x & 31u) == 0u && p) atomicAdd(&Q.c->stat_paths, p);
     if ((threadIdx.x & 31u) == 0u && q) atomicAdd(&Q.c->stat_settled, q);  // primary rays settled in start() without a traversal: counted apart
@@ -517,7 +522,7 @@ struct MrExtendJob
 };
 
 template <int K>
-__global__ void __launch_bounds__(128) k_extend_mr(RenderView V, Queues Q, uint32_t it, int sort, MrOpts mo)
+__global__ void __launch_bounds__(128) k_extend_mr(RenderView V, Queues Q, uint32_t it, int sort, MrOpts mo, int part)
 {
     WfSet& S = Q.c->set[it % 3u];
     const uint32_t n_cont = S.n_cont, n_term = S.n_term;
@@ -527,7 +532,7 @@ __global__ void __launch_bounds__(128) k_extend_mr(RenderView V, Queues Q, uint3
         if (n_cont + n_term) Q.c->stat_iters += 1;
     }
     MrExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort};
-    mr_persistent_trace<0, K>(V.S, job, &S.cur_extend, n_cont + n_term, mo.free_quorum, mo.qn, mo.ql, mo.qi);
+    mr_persistent_trace<0, K>(V.S, job, &S.cur_extend, part == 1 ? n_cont : n_cont + n_term, mo.free_quorum, mo.qn, mo.ql, mo.qi);
     const unsigned long long p = warp_sum(job.paths), q = warp_sum(job.settled);
     if ((threadIdx.x & 31u) == 0u && p) atomicAdd(&Q.c->stat_paths, p);
     if ((threadIdx.x & 31u) == 0u && q) atomicAdd(&Q.c->stat_settled, q);
@@ -825,9 +830,12 @@ __global__ void __launch_bounds__(128) k_nee_bin(RenderView V, Queues Q, uint32_
 // record accesses are near-sequential.  Q.state holds one flag word per slot: WF_NEXT while a ray was traced for the slot in this
 // iteration (set by the previous shade or by k_extend's regeneration), so that the walk knows which lanes of a group have a hit
 // record.  The host may switch between the two shade kernels at any iteration: both leave valid cont / term / nee queues.
+#ifndef PTB_SHADE_MINBLOCKS
+#define PTB_SHADE_MINBLOCKS 4  // resident blocks per SM of k_shade_ordered = its register cap (4: 64 registers; 5 and 6 measured slower)
+#endif
 constexpr uint32_t SHADE_ROWS = 8, SHADE_GROUPS = SHADE_ROWS * 8;
-template <bool SORT>
-__global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q, uint32_t it)
+template <bool SORT, uint32_t KMASK = 0x3fu, bool MEDIA = true>
+__global__ void __launch_bounds__(256, PTB_SHADE_MINBLOCKS) k_shade_ordered(RenderView V, Queues Q, uint32_t it)
 {
     WfSet& S = Q.c->set[it % 3u];
     WfSet& N = Q.c->set[(it + 1u) % 3u];
@@ -911,7 +919,7 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
             for (uint32_t i = threadIdx.x; i < span_live; i += 256u)
             {
                 const uint32_t slot = sorted[i];
-                const uint32_t flags = shade_slot(V, slot);
+                const uint32_t flags = shade_slot_t<KMASK, MEDIA>(V, slot);
                 Q.state[slot] = flags;
                 n_out += (flags & WF_PROBE_OUT) ? 1u : 0u;
             }
@@ -929,7 +937,7 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
                 const uint32_t slot = gi < n_grp ? grp[gi] * 32u + lane : 0xffffffffu;
                 if (slot < Q.slot_end && (Q.state[slot] & WF_NEXT))
                 {
-                    const uint32_t flags = shade_slot(V, slot);
+                    const uint32_t flags = shade_slot_t<KMASK, MEDIA>(V, slot);
                     Q.state[slot] = flags;
                     n_out += (flags & WF_PROBE_OUT) ? 1u : 0u;
                     ++n_live;
@@ -997,6 +1005,24 @@ __global__ void __launch_bounds__(256, 4) k_shade_ordered(RenderView V, Queues Q
     __syncthreads();
     if (threadIdx.x == 0 && live_total) atomicAdd(&Q.c->stat_extend, (unsigned long long)live_total);
     if (threadIdx.x == 0 && out_total) atomicAdd(&Q.c->stat_probe, (unsigned long long)out_total);
+}
+
+// Scene classes of k_shade_ordered (shade_slot_t): 0 the general body; 1 Lambertian + Emissive, 2 + GGX metal, 3 all six kinds — 1 to 3
+// without media.
+constexpr uint32_t SHADE_KMASK_1 = (1u << PTB_LAMBERTIAN) | (1u << PTB_EMISSIVE), SHADE_KMASK_2 = SHADE_KMASK_1 | (1u << PTB_GGX_METAL);
+static void launch_shade_ordered(bool sort, int cls, int grid, cudaStream_t st, const RenderView& V, const Queues& Q, uint32_t it)
+{
+    switch (cls * 2 + (sort ? 1 : 0))
+    {
+    case 2: k_shade_ordered<false, SHADE_KMASK_1, false><<<grid, 256, 0, st>>>(V, Q, it); break;
+    case 3: k_shade_ordered<true, SHADE_KMASK_1, false><<<grid, 256, 0, st>>>(V, Q, it); break;
+    case 4: k_shade_ordered<false, SHADE_KMASK_2, false><<<grid, 256, 0, st>>>(V, Q, it); break;
+    case 5: k_shade_ordered<true, SHADE_KMASK_2, false><<<grid, 256, 0, st>>>(V, Q, it); break;
+    case 6: k_shade_ordered<false, 0x3fu, false><<<grid, 256, 0, st>>>(V, Q, it); break;
+    case 7: k_shade_ordered<true, 0x3fu, false><<<grid, 256, 0, st>>>(V, Q, it); break;
+    case 1: k_shade_ordered<true><<<grid, 256, 0, st>>>(V, Q, it); break;
+    default: k_shade_ordered<false><<<grid, 256, 0, st>>>(V, Q, it); break;
+    }
 }
 
 // The tail: one thread per remaining slot runs regen -> extend -> shade -> shadow -> probe until the slot has no samples left.
@@ -1536,6 +1562,17 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         shade_sort = __builtin_popcount(kinds & ~2u) >= 2;  // kind 1 = Emissive
     }
     for (int g = 0; g < G; ++g) gr[g].dense = !bin && ctx->opt_dense != 0;
+    // scene class of the slot-ordered shade kernel: the instantiation without the material kinds (and media) the scene does not hold
+    int shade_class = 0;
+    if (ctx->opt_shade_class != 0)
+    {
+        uint32_t kinds = 0;
+        for (const auto& b : ctx->scene.blas_desc) kinds |= 1u << std::min<uint32_t>(b.material.kind, 7u);
+        const bool media = !ctx->scene.volumes.empty();
+        if (!media && !(kinds & ~SHADE_KMASK_1)) shade_class = 1;
+        else if (!media && !(kinds & ~SHADE_KMASK_2)) shade_class = 2;
+        else if (!media && !(kinds & ~0x3fu)) shade_class = 3;
+    }
 
     // multiray kernels (option multiray = 2 / 3 rays per lane, multiray.cuh): dynamic shared memory for the ray records, as many resident
     // blocks per SM as fit (or mr_blocks)
@@ -1613,8 +1650,14 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         {
             const int so = dense ? -1 : (sort ? 1 : 0);
             const int eg = sized_grid(mr_eb, R.bound);
-            if (mr_k == 3) k_extend_mr<3><<<eg, 128, mr_es, gs>>>(V, Q, it, so, mro);
-            else k_extend_mr<2><<<eg, 128, mr_es, gs>>>(V, Q, it, so, mro);
+            const int part = ctx->opt_mr_split ? 1 : 0;
+            if (mr_k == 3) k_extend_mr<3><<<eg, 128, mr_es, gs>>>(V, Q, it, so, mro, part);
+            else k_extend_mr<2><<<eg, 128, mr_es, gs>>>(V, Q, it, so, mro, part);
+            if (part)
+            {
+                k_extend<7><<<sized_grid(7, R.bound), threads, 0, gs>>>(V, Q, it, so, rb, nq, 2);
+                rs.launches += 1;
+            }
         }
         else
         {
@@ -1635,8 +1678,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             }
         }
         PTB_CUDA(ctx, mark(2));
-        if (dense && shade_sort) k_shade_ordered<true><<<shade_grid, 256, 0, gs>>>(V, Q, it);
-        else if (dense) k_shade_ordered<false><<<shade_grid, 256, 0, gs>>>(V, Q, it);
+        if (dense) launch_shade_ordered(shade_sort, shade_class, shade_grid, gs, V, Q, it);
         else k_shade<<<sized_grid(std::max(1, ctx->opt_blocks_per_sm), R.bound), threads, 0, gs>>>(V, Q, it);
         PTB_CUDA(ctx, mark(3));
         rs.launches += 2;

@@ -7,6 +7,13 @@
 #include "exact_math.h"
 #include "layout.h"
 
+// Development switch (A/B builds only): the two large material functions as real calls instead of three inlined copies each.
+#if defined(PTB_SHADE_NOINLINE) && defined(__CUDACC__)
+#define PTB_SHADE_FN __host__ __device__ __noinline__
+#else
+#define PTB_SHADE_FN PTB_HD
+#endif
+
 namespace ptb {
 
 using ex::V3;
@@ -268,7 +275,7 @@ PTB_HD float dielectric_f(float cosine, float eta)  // :477-488
     return schlick(cosine, r * r);
 }
 
-PTB_HD V3 scatter_direction(const Mat& m, Rng& rng, V3 incoming, V3 normal, bool front)
+PTB_SHADE_FN V3 scatter_direction(const Mat& m, Rng& rng, V3 incoming, V3 normal, bool front)
 {
     switch (m.kind)
     {
@@ -301,7 +308,7 @@ struct BsdfPdf
     V3 bsdf;
     float pdf;
 };
-PTB_HD BsdfPdf bsdf_pdf(const Mat& m, V3 incoming, V3 outgoing, V3 normal, bool front)
+PTB_SHADE_FN BsdfPdf bsdf_pdf(const Mat& m, V3 incoming, V3 outgoing, V3 normal, bool front)
 {
     BsdfPdf o;
     switch (m.kind)

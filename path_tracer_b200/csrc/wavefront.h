@@ -212,7 +212,12 @@ PTB_HD uint32_t extend_slot(const RenderView& V, uint32_t slot)
 }
 
 // ---- shade ---------------------------------------------------------------------------------------------------------------
-PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
+// KMASK: material kinds the scene can present (bit k = kind k), MEDIA: the scene has media.  The slot-ordered shade kernel is
+// instantiated for a few scene classes (render.cu): with the kinds a scene does not hold compiled out — the body is 7.5 K instructions
+// with all six kinds and media, and its warps stall on instruction fetch — the same source runs as a third to a half of that.
+// 0x3f / true is the general body; the host never picks a mask that omits a kind of the scene.
+template <uint32_t KMASK, bool MEDIA>
+PTB_HD uint32_t shade_slot_t(const RenderView& V, uint32_t slot)
 {
     const float4 o4 = V.ray[slot].o, d4 = V.ray[slot].d;
     const V3 o = ex::v3(o4.x, o4.y, o4.z), d = ex::v3(d4.x, d4.y, d4.z);
@@ -245,7 +250,15 @@ PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
     const bool front = (info & 0x80000000u) != 0u;
     const uint32_t inst = info & 0x7fffffffu;
     const uint32_t blas = V.S.inst[inst].blas;
-    const Mat mat = load_mat(V.S.mat, blas);
+    Mat mat = load_mat(V.S.mat, blas);
+    if (KMASK != 0x3fu)
+    {
+        // kinds outside the mask do not occur: fold them onto the lowest kind of the mask so that their code is provably dead
+        if (!((KMASK >> mat.kind) & 1u)) mat.kind = (KMASK & 1u) ? 0u : 1u;
+#if defined(__CUDA_ARCH__)
+        __builtin_assume(mat.kind < 6u && ((KMASK >> mat.kind) & 1u));
+#endif
+    }
     Rng rng;
     rng.s = (unsigned long long)V.hit[slot].rng_lo | ((unsigned long long)V.hit[slot].rng_hi << 32);
     const V3 hit_p = ex::ray_at(o, d, t);  // Ray::at (fused, ray.rs:20)
@@ -262,7 +275,7 @@ PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
     bool new_last_delta = last_delta;
 
     // media: integrator.rs:189-205 (volume set iterated in table order)
-    unsigned long long vset = V.volset ? V.volset[slot] : 0ull;
+    unsigned long long vset = (MEDIA && V.volset) ? V.volset[slot] : 0ull;
     if (vset)
     {
         float best_t = 0.0f;
@@ -300,7 +313,7 @@ PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
         }
         else
         {
-            if (mat.volume >= 0 && V.volset)  // integrator.rs:217-227
+            if (MEDIA && mat.volume >= 0 && V.volset)  // integrator.rs:217-227
             {
                 if (front) vset |= (1ull << mat.volume);
                 else vset &= ~(1ull << mat.volume);
@@ -394,6 +407,8 @@ PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot)
     if (flags & (WF_SHADOW | WF_PROBE)) V.ray[slot].o = f4(hit_p.x, hit_p.y, hit_p.z, o4.w);
     return flags | WF_TERM;
 }
+
+PTB_HD uint32_t shade_slot(const RenderView& V, uint32_t slot) { return shade_slot_t<0x3fu, true>(V, slot); }
 
 // ---- shadow --------------------------------------------------------------------------------------------------------------
 // adds the explicit light sample's contribution to *r when the shadow ray is unoccluded (integrator.rs:56-70)
