@@ -10,7 +10,7 @@
 //             the continue / terminated queues of the next iteration
 //   k_nee     both direct-light estimates of a bounce in one thread: any-hit for the explicit light sample, lights-TLAS
 //             closest hit + world any-hit for the BSDF-sampled one; one read-modify-write of the slot's radiance
-// Queue counters live in three rotating sets (iteration it consumes set it%3, fills set (it+1)%3 and clears set (it+2)%3),
+// Queue counters live in four rotating sets (iteration it consumes set it%4, fills set (it+1)%4 and clears set (it+2)%4),
 // so no separate bookkeeping launch is needed.  Compaction between stages is warp ballot / match + one atomicAdd per warp
 // and queue.  When few paths remain (the tail of 1024-bounce paths) a single k_tail launch runs every remaining
 // slot to completion, one thread per slot, instead of thousands of near-empty iterations.
@@ -27,6 +27,8 @@
 
 namespace ptb {
 
+constexpr uint32_t WF_SETS = 4;  // rotating counter sets: iteration it consumes set it % 4, fills (it + 1) % 4, clears (it + 2) % 4; the fourth lets k_nee of iteration
+                                // it (still reading set it % 4) run beside k_extend of iteration it + 1 (which clears set (it + 3) % 4)
 struct WfSet  // 64 B
 {
     uint32_t n_cont, n_term;  // consumed by k_extend (polled by the host: keep first)
@@ -36,7 +38,7 @@ struct WfSet  // 64 B
 };
 struct WfCounters
 {
-    WfSet set[3];
+    WfSet set[WF_SETS];
     unsigned long long stat_extend, stat_shadow, stat_probe, stat_paths, stat_iters, stat_probe_shadow, stat_settled, stat_extend_path;
 };
 
@@ -77,6 +79,8 @@ struct RenderState
     uint32_t* h_flags = nullptr;  // pinned, MAX_GROUPS x POLL_RING x 4 (n_cont, n_term, n_nee, n_grp of every iteration of every group)
     std::vector<cudaStream_t> group_streams;  // streams of the wavefront groups 1.. (group 0 runs on the context stream)
     std::vector<cudaEvent_t> group_events;    // fork / join events
+    std::vector<cudaStream_t> nee_streams;    // per group: the stream k_nee runs on while it overlaps the next iteration's k_extend
+    std::vector<cudaEvent_t> nee_events;      // per group: [2g] shade done, [2g + 1] nee done
     uint32_t log_iters = 0;       // iterations recorded in h_flags by the last ptb_render
     std::vector<cudaEvent_t> poll_events;
     std::vector<cudaEvent_t> prof_events;
@@ -139,7 +143,7 @@ __global__ void __launch_bounds__(128) k_init(RenderView V, Queues Q, const uint
     if ((j & 31u) == 0u) Q.grp[0][j >> 5] = i >> 5;
     if (j == 0)
     {
-        for (int s = 0; s < 3; ++s) Q.c->set[s] = WfSet{};
+        for (uint32_t s = 0; s < WF_SETS; ++s) Q.c->set[s] = WfSet{};
         Q.c->set[0].n_term = Q.npix;
         Q.c->set[0].n_grp = (Q.npix + 31u) >> 5;
     }
@@ -249,21 +253,23 @@ struct ExtendJob
     }
 };
 
-// part 0: the whole queue (continuing slots, then the slots to regenerate); part 2: the regeneration part only — the continuing slots
-// went to k_extend_mr (part 1) in a launch of their own: primary rays are coherent and run faster one per lane, bounce rays two per lane
+// part 0: the whole queue (continuing slots, then the slots to regenerate); part 1: the continuing slots only; part 2: the regeneration
+// part only.  Two-part launches: (a) with the multiray kernels — bounce rays two per lane (k_extend_mr, part 1), primary rays one per lane;
+// (b) thin iterations — part 1 of iteration it + 1 runs beside k_nee of iteration it (a continuing slot's ray does not depend on its
+// pending direct-light rays; a slot to regenerate does: its sample is complete only when they have been added)
 template <int MB, int SSTACK = 0>
 __global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint32_t it, int sort, int refill_below, int node_quorum, int part = 0)
 {
-    WfSet& S = Q.c->set[it % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
     const uint32_t n_cont = S.n_cont, n_term = S.n_term;
-    if (part == 0 && blockIdx.x == 0 && threadIdx.x == 0)
+    if (part != 2 && blockIdx.x == 0 && threadIdx.x == 0)
     {
-        Q.c->set[(it + 2u) % 3u] = WfSet{};  // consumed in iteration it-1, refilled from iteration it+1 on
+        Q.c->set[(it + 2u) % WF_SETS] = WfSet{};  // consumed in iteration it-1, refilled from iteration it+1 on
         if (n_cont + n_term) Q.c->stat_iters += 1;
     }
     ExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort};
     if (part == 2) job.idx0 = n_cont;
-    persistent_trace<0, ExtendJob, false, SSTACK>(V.S, job, part == 2 ? &S.cur_regen : &S.cur_extend, part == 2 ? n_term : n_cont + n_term, refill_below, node_quorum);
+    persistent_trace<0, ExtendJob, false, SSTACK>(V.S, job, part == 2 ? &S.cur_regen : &S.cur_extend, part == 2 ? n_term : (part == 1 ? n_cont : n_cont + n_term), refill_below, node_quorum);
     const unsigned long long p = warp_sum(job.paths), q = warp_sum(job.settled);
     if ((threadIdx.x & 31u) == 0u && p) atomicAdd(&Q.c->stat_paths, p);
     if ((threadIdx.x & 31u) == 0u && q) atomicAdd(&Q.c->stat_settled, q);  // primary rays settled in start() without a traversal: counted apart
@@ -272,12 +278,12 @@ __global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint
 // reference-order variant (binary trees, reference visit order): static chunks of 32, one ray per lane
 __global__ void __launch_bounds__(128) k_extend_bin(RenderView V, Queues Q, uint32_t it)
 {
-    WfSet& S = Q.c->set[it % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
     const uint32_t b = it & 1u;
     const uint32_t n_cont = S.n_cont, n_term = S.n_term;
     if (blockIdx.x == 0 && threadIdx.x == 0)
     {
-        Q.c->set[(it + 2u) % 3u] = WfSet{};
+        Q.c->set[(it + 2u) % WF_SETS] = WfSet{};
         if (n_cont + n_term) Q.c->stat_iters += 1;
     }
     const uint32_t total = n_cont + n_term;
@@ -314,8 +320,8 @@ __global__ void __launch_bounds__(128) k_extend_bin(RenderView V, Queues Q, uint
 
 __global__ void __launch_bounds__(128) k_shade(RenderView V, Queues Q, uint32_t it)
 {
-    WfSet& S = Q.c->set[it % 3u];
-    WfSet& N = Q.c->set[(it + 1u) % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
+    WfSet& N = Q.c->set[(it + 1u) % WF_SETS];
     const uint32_t nb = (it + 1u) & 1u;
     const uint32_t lane = threadIdx.x & 31u;
     uint32_t cnt[7], chunks = 0, total = 0;
@@ -429,7 +435,7 @@ struct NeeJob
 template <int MB, int SSTACK = 0>
 __global__ void __launch_bounds__(128, MB) k_nee(RenderView V, Queues Q, uint32_t it, int refill_below, int node_quorum)
 {
-    WfSet& S = Q.c->set[it % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
     NeeJob job{V, Q};
     persistent_trace<2, NeeJob, false, SSTACK>(V.S, job, &S.cur_nee, S.n_nee, refill_below, node_quorum);
     const unsigned long long a = warp_sum(job.n_shadow), b = warp_sum(job.n_probe), c = warp_sum(job.n_probe_shadow);
@@ -524,11 +530,11 @@ struct MrExtendJob
 template <int K>
 __global__ void __launch_bounds__(128) k_extend_mr(RenderView V, Queues Q, uint32_t it, int sort, MrOpts mo, int part)
 {
-    WfSet& S = Q.c->set[it % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
     const uint32_t n_cont = S.n_cont, n_term = S.n_term;
     if (blockIdx.x == 0 && threadIdx.x == 0)
     {
-        Q.c->set[(it + 2u) % 3u] = WfSet{};
+        Q.c->set[(it + 2u) % WF_SETS] = WfSet{};
         if (n_cont + n_term) Q.c->stat_iters += 1;
     }
     MrExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort};
@@ -632,7 +638,7 @@ struct MrNeeJob
 template <int K>
 __global__ void __launch_bounds__(128) k_nee_mr(RenderView V, Queues Q, uint32_t it, MrOpts mo)
 {
-    WfSet& S = Q.c->set[it % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
     MrNeeJob job{V, Q};
     mr_persistent_trace<2, K>(V.S, job, &S.cur_nee, S.n_nee, mo.free_quorum, mo.qn, mo.ql, mo.qi);
     const unsigned long long a = warp_sum(job.n_shadow), b = warp_sum(job.n_probe), c = warp_sum(job.n_probe_shadow);
@@ -780,7 +786,7 @@ struct PathJob
 template <int MB>
 __global__ void __launch_bounds__(128, MB) k_path(RenderView V, Queues Q, uint32_t it, int refill_below, int node_quorum, int finish_quorum)
 {
-    WfSet& S = Q.c->set[it % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
     PathJob job{V, Q, it & 1u, S.n_cont};
     persistent_trace<2, PathJob, true>(V.S, job, &S.cur_extend, S.n_cont + S.n_term, refill_below, node_quorum, finish_quorum);
     const unsigned long long a = warp_sum(job.n_ext), b = warp_sum(job.n_shadow), c = warp_sum(job.n_probe), d = warp_sum(job.n_probe_shadow), e = warp_sum(job.paths),
@@ -799,7 +805,7 @@ __global__ void __launch_bounds__(128, MB) k_path(RenderView V, Queues Q, uint32
 // reference-order variant: static chunks, one entry per lane
 __global__ void __launch_bounds__(128) k_nee_bin(RenderView V, Queues Q, uint32_t it)
 {
-    WfSet& S = Q.c->set[it % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
     const uint32_t n = S.n_nee;
     const uint32_t lane = threadIdx.x & 31u;
     uint32_t c;
@@ -837,8 +843,8 @@ constexpr uint32_t SHADE_ROWS = 8, SHADE_GROUPS = SHADE_ROWS * 8;
 template <bool SORT, uint32_t KMASK = 0x3fu, bool MEDIA = true>
 __global__ void __launch_bounds__(256, PTB_SHADE_MINBLOCKS) k_shade_ordered(RenderView V, Queues Q, uint32_t it)
 {
-    WfSet& S = Q.c->set[it % 3u];
-    WfSet& N = Q.c->set[(it + 1u) % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
+    WfSet& N = Q.c->set[(it + 1u) % WF_SETS];
     const uint32_t nb = (it + 1u) & 1u;
     const uint32_t* grp = Q.grp[it & 1u];
     uint32_t* out[4] = {Q.term[nb], Q.cont[nb], Q.nee, Q.grp[nb]};
@@ -1029,7 +1035,7 @@ static void launch_shade_ordered(bool sort, int cls, int grid, cudaStream_t st, 
 template <bool BIN>
 __global__ void __launch_bounds__(64) k_tail(RenderView V, Queues Q, uint32_t it)
 {
-    WfSet& S = Q.c->set[it % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
     const uint32_t b = it & 1u;
     const uint32_t n_cont = S.n_cont, n_term = S.n_term;
     const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1085,7 +1091,7 @@ __global__ void __launch_bounds__(64) k_tail(RenderView V, Queues Q, uint32_t it
 template <bool BIN>
 __global__ void __launch_bounds__(96) k_tail_roles(RenderView V, Queues Q, uint32_t it, uint32_t spb)
 {
-    WfSet& S = Q.c->set[it % 3u];
+    WfSet& S = Q.c->set[it % WF_SETS];
     const uint32_t b = it & 1u;
     const uint32_t n_cont = S.n_cont, n_term = S.n_term;
     const uint32_t lane = threadIdx.x & 31u, role = threadIdx.x >> 5;
@@ -1232,6 +1238,8 @@ void render_state_destroy(ptb_context* ctx)
     for (auto e : rs->prof_events) cudaEventDestroy(e);
     for (auto e : rs->group_events) cudaEventDestroy(e);
     for (auto s : rs->group_streams) cudaStreamDestroy(s);
+    for (auto s : rs->nee_streams) cudaStreamDestroy(s);
+    for (auto e : rs->nee_events) cudaEventDestroy(e);
     if (rs->ev_begin) cudaEventDestroy(rs->ev_begin);
     if (rs->ev_end) cudaEventDestroy(rs->ev_end);
     if (rs->h_flags) cudaFreeHost(rs->h_flags);
@@ -1475,10 +1483,25 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         PTB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         rs.group_events.push_back(e);
     }
+    // k_nee beside the next iteration's k_extend (thin iterations; option nee_overlap): needs a stream and two events per group
+    const bool overlap_on = !prof && !bin && ctx->opt_nee_overlap != 0 && enable_nee;
+    while (overlap_on && (int)rs.nee_streams.size() < G)
+    {
+        cudaStream_t s2;
+        PTB_CUDA(ctx, cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking));
+        rs.nee_streams.push_back(s2);
+        for (int k = 0; k < 2; ++k)
+        {
+            cudaEvent_t e;
+            PTB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            rs.nee_events.push_back(e);
+        }
+    }
     struct GroupRun
     {
         Queues Q;
         cudaStream_t st;
+        bool nee_pending = false;  // a k_nee of this group runs on its own stream: whatever needs its results waits for nee_events[2g + 1]
         uint32_t it = 0;
         bool dense = false, done = false;
         uint32_t* h_flags = nullptr;
@@ -1588,6 +1611,8 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     // thin iterations (fewer live slots than mr_min_per_lane per resident lane of the one-ray kernels) go to the one-ray-per-lane kernels:
     // a lane that holds one ray only waits at every gate
     const uint32_t mr_min = (uint32_t)std::max(0, ctx->opt_mr_min_per_lane) * (uint32_t)(ctx->sm_count * 7 * 128);
+    // k_nee beside the next iteration's k_extend once a group's live slots are below nee_overlap per lane of the one-ray grid (0 = never)
+    const uint32_t ov_below = ctx->opt_nee_overlap < 0 ? 0xffffffffu : (uint32_t)ctx->opt_nee_overlap * (uint32_t)(ctx->sm_count * 7 * 128);
     if (mr_k)
     {
         if (mr_k == 3)
@@ -1645,7 +1670,25 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         const uint32_t it = R.it;
         const bool dense = R.dense;
         const int rb = ctx->opt_refill_below, rbn = ctx->opt_nee_refill_below, nq = ctx->opt_node_quorum;
+        // thin iterations: k_nee of iteration it on its own stream, beside part 1 (continuing slots) of iteration it + 1's k_extend
+        const bool ov = overlap_on && R.bound < ov_below && !(mr_k && R.bound >= mr_min);
+        cudaStream_t ns = overlap_on ? rs.nee_streams[g] : gs;
+        auto join_nee = [&]() -> cudaError_t {
+            if (!R.nee_pending) return cudaSuccess;
+            R.nee_pending = false;
+            return cudaStreamWaitEvent(gs, rs.nee_events[2 * g + 1], 0);
+        };
+        if (!ov) PTB_CUDA(ctx, join_nee());
         if (bin) k_extend_bin<<<grid, threads, 0, gs>>>(V, Q, it);
+        else if (ov)
+        {
+            const int so = dense ? -1 : (sort ? 1 : 0);
+            const int eg = sized_grid(7, R.bound);
+            k_extend<7><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq, 1);
+            PTB_CUDA(ctx, join_nee());  // a slot to regenerate is complete only with its last direct-light rays
+            k_extend<7><<<eg, threads, 0, gs>>>(V, Q, it, so, rb, nq, 2);
+            rs.launches += 1;
+        }
         else if (mr_k && R.bound >= mr_min)
         {
             const int so = dense ? -1 : (sort ? 1 : 0);
@@ -1685,6 +1728,14 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         if (V.enable_nee)
         {
             if (bin) k_nee_bin<<<grid, threads, 0, gs>>>(V, Q, it);
+            else if (ov)
+            {
+                PTB_CUDA(ctx, cudaEventRecord(rs.nee_events[2 * g], gs));
+                PTB_CUDA(ctx, cudaStreamWaitEvent(ns, rs.nee_events[2 * g], 0));
+                k_nee<8><<<sized_grid(8, R.bound), threads, 0, ns>>>(V, Q, it, rbn, nq);
+                PTB_CUDA(ctx, cudaEventRecord(rs.nee_events[2 * g + 1], ns));
+                R.nee_pending = true;
+            }
             else if (mr_k && R.bound >= mr_min)
             {
                 const int ng = sized_grid(mr_nb, R.bound);
@@ -1714,7 +1765,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         }
         PTB_CUDA(ctx, cudaGetLastError());
         // active-slot count of the next iteration, read LAG iterations behind the launch front
-        PTB_CUDA(ctx, cudaMemcpyAsync(&R.h_flags[(it % POLL_RING) * 4], &Q.c->set[(it + 1u) % 3u].n_cont, 16, cudaMemcpyDeviceToHost, gs));
+        PTB_CUDA(ctx, cudaMemcpyAsync(&R.h_flags[(it % POLL_RING) * 4], &Q.c->set[(it + 1u) % WF_SETS].n_cont, 16, cudaMemcpyDeviceToHost, gs));
         PTB_CUDA(ctx, cudaEventRecord(rs.poll_events[(size_t)g * NEV + it % NEV], gs));
         if (g == 0) rs.log_iters = it + 1;
         R.it = it + 1;
@@ -1724,11 +1775,12 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             const uint32_t* f = &R.h_flags[((it - LAG) % POLL_RING) * 4];
             const uint32_t active = f[0] + f[1];
             R.bound = active;
-            if (active == 0u) { R.done = true; return PTB_OK; }
+            if (active == 0u) { R.done = true; return PTB_OK; }  // a pending k_nee is joined with the group (below)
             const bool to_path = active <= path_threshold;
             const bool to_tail = !to_path && active <= tail_threshold;
             // live slots scattered thinly over the listed groups: the queue shade kernel from the next iteration on (the queues are valid as they are)
             if (dense && (uint64_t)active * 100u < dense_pct * 32u * (uint64_t)f[3]) R.dense = false;
+            if (to_path || to_tail) PTB_CUDA(ctx, join_nee());
             if (to_path)
             {
                 const int rc = launch_path(g, it + 1u);
@@ -1754,6 +1806,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     // error exit from the launch loop: kernels of the forked group streams may still be running — drain them before handing the
     // context back, or a later call on ctx->stream would race with them
     auto abandon = [&](int rc) -> int {
+        for (auto ns : rs.nee_streams) cudaStreamSynchronize(ns);
         for (int g = 1; g < G; ++g) cudaStreamSynchronize(gr[g].st);
         cudaStreamSynchronize(st);
         return rc;
@@ -1775,6 +1828,8 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             if (!gr[g].done) ++running;
         }
     }
+    for (int g = 0; g < G; ++g)
+        if (gr[g].nee_pending) PTB_CUDA(ctx, cudaStreamWaitEvent(gr[g].st, rs.nee_events[2 * g + 1], 0));
     for (int g = 1; g < G; ++g)  // join
     {
         PTB_CUDA(ctx, cudaEventRecord(rs.group_events[g], gr[g].st));
