@@ -29,7 +29,7 @@ enum : int
     MR_GX = 11, MR_GY = 12,              // inner children of the current node still to visit
     MR_SP = 13,                          // sp | blas_sp << 8
     MR_INST = 14,                        // InstanceRow index while inside a BLAS
-    MR_FL = 15,                          // lh | lmask << 8 | oi << 16 | oiw << 19 | any << 22 | in_blas << 23
+    MR_FL = 15,                          // lh | lmask << 8 | oi << 16 | oiw << 19 | any << 22 | in_blas << 23; bits 24.. are the job's (the traversal keeps them)
     MR_HUD = 16, MR_HVD = 17, MR_HDET = 18, MR_HSLOT = 19, MR_HINST = 20,
     MR_INVW = 21,                        // exact reciprocal of the world-space direction
     MR_JOB = 24                          // first word of the job's own per-ray data

@@ -546,7 +546,13 @@ __global__ void __launch_bounds__(128) k_extend_mr(RenderView V, Queues Q, uint3
 
 struct MrNeeJob
 {
-    static constexpr int JOBW = 4;  // [0] nee queue entry (slot | flags), [1] stage, [2] t of the light hit (stage 1), [3] its instance
+    static constexpr int JOBW = 3;  // [0] nee queue entry (slot | flags), [1] t of the light hit (stage 1), [2] its instance; the stage (0 shadow ray, 1 light
+                                    // probe, 2 probe visibility) rides in bits 24-25 of the record's flag word, which the traversal leaves alone
+    static constexpr uint32_t STAGE_SHIFT = 24;
+    template <class R>
+    __device__ __forceinline__ uint32_t stage_of(const R& r) const { return (r.ld(MR_FL) >> STAGE_SHIFT) & 3u; }
+    template <class R>
+    __device__ __forceinline__ void set_stage(const R& r, uint32_t stage) const { r.st(MR_FL, r.ld(MR_FL) | (stage << STAGE_SHIFT)); }  // after mr_begin (which rewrites the word)
     const RenderView& V;
     const Queues& Q;
     unsigned long long n_shadow = 0, n_probe = 0, n_probe_shadow = 0;
@@ -562,7 +568,7 @@ struct MrNeeJob
     {
         const uint32_t slot = r.ld(MR_JOB) & NEE_SLOT_MASK;
         *o = origin(r);
-        const float4 d4 = r.ld(MR_JOB + 1) == 0u ? V.shadow[slot].d : V.probe[slot].d;
+        const float4 d4 = stage_of(r) == 0u ? V.shadow[slot].d : V.probe[slot].d;
         *d = ex::v3(d4.x, d4.y, d4.z);
     }
     template <class R>
@@ -572,8 +578,9 @@ struct MrNeeJob
         const V3 d = ex::v3(d4.x, d4.y, d4.z);
         ++n_probe;
         if (!tlas_may_hit(V.S, 1, o, d)) return MT_IDLE;
-        r.st(MR_JOB + 1, 1u);
-        return mr_begin(r, V.S, 1, o, d, ex::inf(), false);
+        const uint32_t t = mr_begin(r, V.S, 1, o, d, ex::inf(), false);
+        set_stage(r, 1u);
+        return t;
     }
     template <class R>
     __device__ __forceinline__ uint32_t start(uint32_t idx, const R& r)
@@ -585,9 +592,8 @@ struct MrNeeJob
         if (e & NEE_SHADOW_BIT)
         {
             const float4 d4 = V.shadow[slot].d;
-            r.st(MR_JOB + 1, 0u);
             ++n_shadow;
-            return mr_begin(r, V.S, 0, o, ex::v3(d4.x, d4.y, d4.z), d4.w, true);
+            return mr_begin(r, V.S, 0, o, ex::v3(d4.x, d4.y, d4.z), d4.w, true);  // stage 0
         }
         return begin_probe(r, slot, o);
     }
@@ -602,7 +608,7 @@ struct MrNeeJob
     __device__ __forceinline__ uint32_t finish(const R& r, bool mine)
     {
         if (!mine) return MT_IDLE;
-        const uint32_t e = r.ld(MR_JOB), slot = e & NEE_SLOT_MASK, stage = r.ld(MR_JOB + 1);
+        const uint32_t e = r.ld(MR_JOB), slot = e & NEE_SLOT_MASK, stage = stage_of(r);
         const bool hit = r.ld(MR_HINST) != TRAV_NONE;
         if (stage == 0u)
         {
@@ -618,17 +624,18 @@ struct MrNeeJob
             if (hit)
             {
                 const float lt = r.ldf(MR_TMAX);
-                r.stf(MR_JOB + 2, lt);
-                r.st(MR_JOB + 3, r.ld(MR_HINST));
-                r.st(MR_JOB + 1, 2u);
+                r.stf(MR_JOB + 1, lt);
+                r.st(MR_JOB + 2, r.ld(MR_HINST));
                 ++n_probe_shadow;
-                return mr_begin(r, V.S, 0, origin(r), r.ld3(MR_D), lt * (1.0f - ex::EPS), true, true);  // MR_D: the probe direction, back in world space
+                const uint32_t t = mr_begin(r, V.S, 0, origin(r), r.ld3(MR_D), lt * (1.0f - ex::EPS), true, true);  // MR_D: the probe direction, back in world space
+                set_stage(r, 2u);
+                return t;
             }
         }
         else if (!hit)
         {
             const float4 d4 = V.probe[slot].d;
-            const V3 c = probe_light_contrib(V, slot, ex::v3(d4.x, d4.y, d4.z), r.ldf(MR_JOB + 2), mr_hit_u(r), mr_hit_v(r), V.S.tri_prim[r.ld(MR_HSLOT)], r.ld(MR_JOB + 3));
+            const V3 c = probe_light_contrib(V, slot, ex::v3(d4.x, d4.y, d4.z), r.ldf(MR_JOB + 1), mr_hit_u(r), mr_hit_v(r), V.S.tri_prim[r.ld(MR_HSLOT)], r.ld(MR_JOB + 2));
             add_radiance(slot, c.x, c.y, c.z);
         }
         return MT_IDLE;

@@ -44,6 +44,31 @@ def test_traversal_matches_oracle(po, scenes, emu, name):
     assert ties < 200
 
 
+@pytest.mark.parametrize("name", ["c2", "c1", "c3_small", "materials", "c4_small"])
+def test_multiray_stage_logic_matches_one_ray_traversal(po, scenes, emu, name):
+    """multiray.cuh (K rays per lane, gated stages, ray records addressed through MrRay) on one emulated warp against the one-ray
+    traversal of traverse.h: the per-ray arithmetic and visit order are the same, so every output is bit-identical, whatever K and the
+    quorums — and the oracle's any-hit answers are reproduced."""
+    sd = {"c1": scenes.scene_c1, "c2": scenes.scene_c2, "c3_small": lambda: scenes.scene_c3(grid=8), "materials": scenes.scene_materials_test,
+          "c4_small": lambda: scenes.scene_c4(nverts=150, n_spheres=8)}[name]()
+    sc = po.OracleScene(sd)
+    es = emu.EmuScene(sd, po.pack_scene)
+    for _, o, d, tm in _batches(po, scenes, sd, 6000):
+        for which in (0, 1):
+            ref = es.trace(o, d, tm, which=which, kernel=0)
+            ref_any = sc.trace_any(o, d, tm, which=which)
+            for K, fq, qn, ql, qi in ((1, 24, 8, 1, 1), (2, 24, 12, 8, 8), (3, 8, 1, 1, 1), (4, 100, 32, 32, 32)):
+                got = emu.trace_mr(es, o, d, tm, which=which, K=K, free_quorum=fq, qn=qn, ql=ql, qi=qi)
+                assert np.array_equal(got["hit"], ref["hit"]), (name, which, K)
+                m = ref["hit"] > 0
+                for key in ("prim", "inst"):
+                    assert np.array_equal(got[key][m], ref[key][m]), (name, which, K, key)
+                for key in ("t", "u", "v"):
+                    assert np.array_equal(bits(got[key][m]), bits(ref[key][m])), (name, which, K, key)
+                ga = emu.trace_mr(es, o, d, tm, which=which, any_hit=True, K=K, free_quorum=fq, qn=qn, ql=ql, qi=qi)
+                assert np.array_equal(ga["hit"], ref_any["hit"]), (name, which, K, "any")
+
+
 def test_integer_tier_bit_exact(po, emu):
     idx = (np.arange(20000, dtype=np.uint32) * 7) % 5
     seeds = (np.arange(20000, dtype=np.uint32) * np.uint32(2654435761)).astype(np.uint32)
