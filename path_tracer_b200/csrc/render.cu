@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(128) k_init(RenderView V, Queues Q, const uint
     V.ray[i].d.w = 0.0f;  // samples started = 0
     V.accum[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     if (V.accum_sq) V.accum_sq[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    V.id[i] = V.K == 1u ? id_px[i] : 0u;  // one slot per pixel: the slot continues the pixel's id history (main.rs:206)
+    V.id[i] = V.K == 1u ? id_px[slot_pixel(V, i)] : 0u;  // one slot per pixel: the slot continues the pixel's id history (main.rs:206)
     Q.term[0][j] = i;
     Q.state[i] = WF_TERM;
     if ((j & 31u) == 0u) Q.grp[0][j >> 5] = i >> 5;
@@ -155,10 +155,11 @@ __global__ void __launch_bounds__(256) k_combine(RenderView V, float4* accum_px,
 {
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= V.npix) return;
+    const uint32_t j = pixel_slot(V, p);  // the pixel's slot index within a layer
     float4 a = accum_px[p];
     for (uint32_t k = 0; k < V.K; ++k)
     {
-        const float4 b = V.accum[(size_t)k * V.npix + p];
+        const float4 b = V.accum[(size_t)k * V.npix + j];
         a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
     }
     accum_px[p] = a;
@@ -167,18 +168,18 @@ __global__ void __launch_bounds__(256) k_combine(RenderView V, float4* accum_px,
         float4 q = accum_sq_px[p];
         for (uint32_t k = 0; k < V.K; ++k)
         {
-            const float4 b = V.accum_sq[(size_t)k * V.npix + p];
+            const float4 b = V.accum_sq[(size_t)k * V.npix + j];
             q.x += b.x; q.y += b.y; q.z += b.z; q.w += b.w;
         }
         accum_sq_px[p] = q;
     }
     const uint32_t k_last = (sample_count - 1u) % V.K;
-    position_px[p] = V.position[(size_t)k_last * V.npix + p];
-    if (V.K == 1u) id_px[p] = V.id[p];
+    position_px[p] = V.position[(size_t)k_last * V.npix + j];
+    if (V.K == 1u) id_px[p] = V.id[j];
     else
     {
         const uint32_t k_prev = (sample_count - 2u) % V.K;  // K <= sample_count, so sample_count >= 2 here
-        id_px[p] = ((V.id[(size_t)k_prev * V.npix + p] & 0xffffu) << 16) | (V.id[(size_t)k_last * V.npix + p] & 0xffffu);
+        id_px[p] = ((V.id[(size_t)k_prev * V.npix + j] & 0xffffu) << 16) | (V.id[(size_t)k_last * V.npix + j] & 0xffffu);
     }
 }
 
@@ -1455,6 +1456,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     V.cam = cam_dev(ctx);
     V.W = rs.W; V.H = rs.H;
     V.npix = rs.npix;
+    V.tiles_x = (ctx->opt_tile_pixels && rs.W % 8u == 0u && rs.H % 4u == 0u) ? rs.W / 8u : 0u;
     V.K = K;
     V.sample_begin = sample_begin; V.sample_count = sample_count;
     V.seed = seed;

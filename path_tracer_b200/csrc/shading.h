@@ -111,10 +111,12 @@ PTB_HD uint32_t low_bias_hash(uint32_t x)                                       
 }
 // dimension 1 of the table (sampling.rs:24-30): XOR of direction numbers over the set bits of the index.
 // DIRECTIONS[b] (sampling.rs:4-8) is the Sobol dimension-2 generator v_b = v_{b-1} ^ (v_{b-1} >> 1), v_0 = 1<<31.
+// BITS: the index is known to be below 2^BITS (get_ss_sobol reduces it modulo NUM_POINTS = 512 first: 9 of the 32 rounds do the work).
+template <int BITS = 32>
 PTB_HD uint32_t sobol_dim1(uint32_t index)
 {
     uint32_t x = 0, v = 0x80000000u;
-    for (int b = 0; b < 32; ++b)
+    for (int b = 0; b < BITS; ++b)
     {
         if ((index >> b) & 1u) x ^= v;
         v ^= v >> 1;
@@ -127,9 +129,10 @@ PTB_HD void ss_sobol(uint32_t index, uint32_t seed, float* px, float* py)
 {
     const uint32_t x_seed = low_bias_hash(seed), y_seed = low_bias_hash(seed + 1u), shuffle_seed = low_bias_hash(seed + 2u);
     const uint32_t i = scramble_base2(index, shuffle_seed) % SOBOL_POINTS;
-    const uint32_t x = scramble_base2(rev32(i), x_seed), y = scramble_base2(sobol_dim1(i), y_seed);
-    *px = ex::div((float)x, 4294967296.0f);
-    *py = ex::div((float)y, 4294967296.0f);
+    const uint32_t x = scramble_base2(rev32(i), x_seed), y = scramble_base2(sobol_dim1<9>(i), y_seed);  // i < 512
+    // x as f32 / 2^32 (sampling.rs:112-113): a division by a power of two is exact, so is the product with 2^-32
+    *px = ex::mul((float)x, 2.3283064365386963e-10f);
+    *py = ex::mul((float)y, 2.3283064365386963e-10f);
 }
 
 // ---- camera.rs:94-105 ------------------------------------------------------------------------------------------------------

@@ -57,7 +57,9 @@ struct RenderView
     CameraDev cam;
     uint32_t W, H;
     uint32_t npix;           // W * H
-    uint32_t K;              // slots per pixel: slot = k * npix + pixel renders the samples k, k + K, k + 2K, ... of its pixel
+    uint32_t K;              // slots per pixel: slot = k * npix + j renders the samples k, k + K, k + 2K, ... of pixel slot_pixel(j)
+    uint32_t tiles_x;        // > 0: slots are laid over the frame in tiles of 8 x 4 pixels (W / 8 tiles per row), so that the 32 rays of a warp
+                             // cover a compact patch of the image instead of a 32 x 1 line; 0: j = pixel (frame sizes that do not divide)
     uint32_t sample_begin, sample_count;
     unsigned long long seed;
     uint32_t max_bounces;
@@ -82,6 +84,21 @@ enum : uint32_t { WF_NEXT = 1u, WF_TERM = 2u, WF_SHADOW = 4u, WF_PROBE = 8u,
 constexpr uint32_t ST_LAST_DELTA = 1u << 24, ST_HAS_SAMPLE = 1u << 25, ST_BOUNCE_MASK = (1u << 24) - 1u;
 constexpr uint32_t NEE_SHADOW_BIT = 0x80000000u, NEE_PROBE_BIT = 0x40000000u, NEE_SLOT_MASK = 0x3fffffffu;  // nee queue entry = slot | flags
 constexpr uint32_t Q_MISS = 6;  // shade queue kinds: 0..5 = material kinds, 6 = miss
+
+// slot index within a layer -> pixel, and back (bijections; identity when tiles_x == 0)
+PTB_HD uint32_t slot_pixel(const RenderView& V, uint32_t j)
+{
+    if (V.tiles_x == 0u) return j;
+    const uint32_t tile = j >> 5, in = j & 31u;
+    const uint32_t x = (tile % V.tiles_x) * 8u + (in & 7u), y = (tile / V.tiles_x) * 4u + (in >> 3);
+    return y * V.W + x;
+}
+PTB_HD uint32_t pixel_slot(const RenderView& V, uint32_t p)
+{
+    if (V.tiles_x == 0u) return p;
+    const uint32_t x = p % V.W, y = p / V.W;
+    return (((y >> 2) * V.tiles_x + (x >> 3)) << 5) | ((y & 3u) << 3) | (x & 7u);
+}
 
 PTB_HD float4 f4(float x, float y, float z, float w)
 {
@@ -118,7 +135,7 @@ PTB_HD uint32_t regen_slot(const RenderView& V, uint32_t slot, V3* o_out, V3* d_
             V.accum_sq[slot] = q;
         }
     }
-    const uint32_t pixel = slot % V.npix, sub = slot / V.npix;
+    const uint32_t pixel = slot_pixel(V, slot % V.npix), sub = slot / V.npix;
     const uint32_t local = sub + started * V.K;  // index of the slot's next sample within this render call
     if (local >= V.sample_count)
     {

@@ -13,7 +13,19 @@ rd, wr, dur = row("dram__bytes_read.sum"), row("dram__bytes_write.sum"), row("gp
 tot = [a + b for a, b in zip(rd, wr)]
 p = "profiles/traffic.json"
 j = json.load(open(p))
-j[wl] = {"k_extend_dram_bytes_per_launch": tot[0], "k_shade_dram_bytes_per_launch": tot[1], "k_nee_dram_bytes_per_launch": tot[2],
+names = [k.strip().strip("'") for k in kern.strip("[]").split("', '")]
+def col(prefix, skip=()):  # first captured launch of a kernel by name (an iteration is three or, with the multiray kernels, four launches)
+    for i, k in enumerate(names):
+        if prefix in k and not any(x in k for x in skip):
+            return i
+    return None
+ie = col("k_extend")
+ish, ine = col("k_shade"), col("k_nee")
+j[wl] = {"k_extend_dram_bytes_per_launch": tot[ie], "k_shade_dram_bytes_per_launch": tot[ish], "k_nee_dram_bytes_per_launch": tot[ine],
          "captured_launch_duration": " / ".join(f"{d:.6g} ms" for d in dur), "kernels": kern, "source": path, "note": note}
+ie2 = [i for i, k in enumerate(names) if "k_extend" in k and i != ie]
+if ie2:
+    j[wl]["k_extend_part2_dram_bytes_per_launch"] = tot[ie2[0]]
+    j[wl]["note_parts"] = "k_extend is launched in two parts with the multiray kernels: continuing slots (k_extend_mr, the column reported as k_extend) and slots to regenerate (k_extend<7>, part 2)"
 json.dump(j, open(p, "w"), indent=1)
 print(j[wl])
