@@ -240,6 +240,9 @@ int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, floa
  *                     waiting for the node / leaf / instance stage before a warp runs it; mr_free_quorum (24): finished or idle ray
  *                     slots of a warp that trigger a refill; mr_blocks: resident blocks per SM (0 = what fits); mr_min_per_lane (16):
  *                     iterations with fewer live slots per lane of the one-ray grid run the one-ray kernels
+ *   tile_pixels       1 (default): path slots are laid over the frame in tiles of 8 x 4 pixels, so that the 32 rays of a warp cover a compact
+ *                     patch of the image instead of a 32 x 1 line (frames whose width divides by 8 and height by 4; same results bit for
+ *                     bit, 1 - 1.5 % per frame); 0: row-major
  *   nee_overlap       thin iterations (fewer live slots than this many per lane of the one-ray grid; 0 never = default, < 0 always): k_nee
  *                     of iteration i runs on a stream of its own beside the continuing slots' part of iteration i + 1's k_extend — a
  *                     continuing slot's next ray does not depend on its pending direct-light rays (same results; measured without gain: the thin iterations are issue-bound work on hard rays)
