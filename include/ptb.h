@@ -232,7 +232,8 @@ int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, floa
  *                     all kinds, each without media; the kinds a scene does not hold are compiled out) or the general body (0)
  *   sort_materials    queue shade kernel: one queue per material kind (default 1)
  *   extend_blocks, nee_blocks   resident blocks per SM (= register cap) of k_extend (5..8, default 7) / k_nee (4..8, default 8)
- *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit 8, any-hit 8)
+ *   refill_below, nee_refill_below   lanes of a warp still traversing below which idle lanes take new rays (closest-hit: < 0 = default, 4 with the
+ *                     multiray kernels, else 8; any-hit 8)
  *   node_quorum       lanes that must want the node stage before it runs (default 8)
  *   multiray          rays per lane of k_extend / k_nee: 0 one (persist.cuh), 2 / 3 the multiray kernels (csrc/multiray.cuh: a lane owns
  *                     K rays, the thin stages run once enough lanes hold a ray waiting for them), < 0 automatic (default): 2 for scenes
@@ -252,7 +253,7 @@ int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, floa
  *                     side by side; 0: one thread per slot runs them in sequence (same results)
  *   tail_slots_per_block   slots per three-warp block of that kernel, 1..32 (default 32; same results)
  *   wavefront_groups  independent wavefronts per render, each over 1/G of the slots with its own queues on its own stream,
- *                     1..8 (default 2; bit-identical results for every G; forced to 1 while profiling is on)
+ *                     1..8 (default < 0: 1 with the multiray kernels, else 2; bit-identical results for every G; forced to 1 while profiling is on)
  *   path_threshold    active slots at which ALL remaining slots go to the persistent path kernel k_path (extend -> shade -> NEE
  *                     rays -> next bounce chained per lane in one launch); 0 = never (default: measured slower than thin wavefront
  *                     iterations + tail kernel), < 0 automatic; path_blocks (4..6) and finish_quorum (1..32,

@@ -89,7 +89,7 @@ struct ptb_context
     int opt_extend_kernel = 0;  // 0 wide, 1 reference-order
     int opt_block_threads = 128;
     int opt_blocks_per_sm = 8;
-    int opt_refill_below = 8, opt_nee_refill_below = 8;    // persistent kernels refill idle lanes when fewer than this many lanes of a warp are traversing
+    int opt_refill_below = -1, opt_nee_refill_below = 8;   // persistent kernels refill idle lanes when fewer than this many lanes of a warp are traversing
     int opt_shade_class = -1;     // k_shade_ordered instantiated for the scene's material kinds (-1, default) or the general body (0)
     int opt_multiray = -1;        // rays per lane of k_extend / k_nee: 0 = one (persist.cuh), 2 / 3 = multiray.cuh, -1 = by scene size (render.cu)
     int opt_tile_pixels = 1;      // slots laid over the frame in 8 x 4 pixel tiles (a warp's 32 rays cover a compact patch) instead of row-major lines
@@ -100,7 +100,7 @@ struct ptb_context
     int opt_node_quorum = 8;      // lanes of a warp that must want the node stage before it runs (1 = never postponed)
     int opt_extend_blocks = 7, opt_nee_blocks = 8;  // resident blocks per SM (launch bounds -> register cap) of k_extend / k_nee
     int opt_slots_per_pixel = 16;  // path slots per pixel (1..16): more slots = more paths in flight, fewer and larger wavefront iterations
-    int opt_wavefront_groups = 2; // independent wavefronts per render, each over 1/G of the slots on its own stream (1..8)
+    int opt_wavefront_groups = -1; // independent wavefronts per render, each over 1/G of the slots on its own stream (1..8; < 0: 1 with the multiray kernels, else 2)
     int opt_dense = 1;            // slot-ordered wavefront kernels while most slots are live (0 = queue kernels throughout)
     int opt_dense_threshold = 60; // live slots per listed 32-slot group, in percent, below which ptb_render continues with the queue kernels
     int opt_shade_sort = -1;      // k_shade_ordered sorts each span's slots by shade kind: 1 yes, 0 no, <0 automatic (scenes with >= 2 surface material kinds)

@@ -93,7 +93,7 @@ int ptb_trace_closest_static(ptb_context* ctx, int which, uint64_t n, const floa
     PTB_CUDA(ctx, cudaMemcpyAsync(base + OFF_D, d3, n * 12, cudaMemcpyHostToDevice, st));
     PTB_CUDA(ctx, cudaMemcpyAsync(base + OFF_TMAX, tmax, n * 4, cudaMemcpyHostToDevice, st));
     // the 8-wide persistent kernel; launch_trace clears the cursor (the one part of the scratch that must start at zero) before the launch
-    PTB_CUDA(ctx, launch_trace(ctx->S, which, 0, 0, n, a, ctx->sm_count, st, ctx->opt_refill_below, ctx->opt_node_quorum));
+    PTB_CUDA(ctx, launch_trace(ctx->S, which, 0, 0, n, a, ctx->sm_count, st, ctx->opt_refill_below < 0 ? 8 : ctx->opt_refill_below, ctx->opt_node_quorum));
 #define DL(dst, off, bytes) \
     if (dst) PTB_CUDA(ctx, cudaMemcpyAsync(dst, base + off, bytes, cudaMemcpyDeviceToHost, st))
     DL(hit, OFF_HIT, n);

@@ -354,7 +354,7 @@ int ptb_trace_resident(ptb_context* ctx, int which, int kernel, int any_hit, int
     PTB_CUDA(ctx, cudaEventCreate(&e1));
     TraceArgs a = trace_args(ctx);
     PTB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
-    for (int r = 0; r < repeats; ++r) PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, any_hit, ctx->t_n, a, ctx->sm_count, ctx->stream, any_hit ? ctx->opt_nee_refill_below : ctx->opt_refill_below, ctx->opt_node_quorum, ctx->opt_mr));
+    for (int r = 0; r < repeats; ++r) PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, any_hit, ctx->t_n, a, ctx->sm_count, ctx->stream, any_hit ? ctx->opt_nee_refill_below : (ctx->opt_refill_below < 0 ? 8 : ctx->opt_refill_below), ctx->opt_node_quorum, ctx->opt_mr));
     PTB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
     PTB_CUDA(ctx, cudaEventSynchronize(e1));
     float ms = 0;
@@ -389,7 +389,7 @@ int ptb_trace_closest(ptb_context* ctx, int which, int kernel, uint64_t n, const
     if (n == 0) return PTB_OK;  // empty batch
     int rc = ptb_trace_upload(ctx, n, o3, d3, tmax);
     if (rc != PTB_OK) return rc;
-    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 0, n, trace_args(ctx), ctx->sm_count, ctx->stream, ctx->opt_refill_below, ctx->opt_node_quorum, ctx->opt_mr));
+    PTB_CUDA(ctx, launch_trace(ctx->S, which, kernel, 0, n, trace_args(ctx), ctx->sm_count, ctx->stream, ctx->opt_refill_below < 0 ? 8 : ctx->opt_refill_below, ctx->opt_node_quorum, ctx->opt_mr));
 #define DL(dst, src, bytes) \
     if (dst) PTB_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream))
     DL(hit, ctx->t_hit.p, n);
@@ -460,7 +460,7 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "shade_sort") ctx->opt_shade_sort = value;
     else if (n == "dense_threshold") ctx->opt_dense_threshold = value;
     else if (n == "nee_refill_below") ctx->opt_nee_refill_below = value < 1 ? 1 : (value > 32 ? 32 : value);
-    else if (n == "refill_below") ctx->opt_refill_below = value < 1 ? 1 : (value > 32 ? 32 : value);
+    else if (n == "refill_below") ctx->opt_refill_below = value < 0 ? -1 : (value < 1 ? 1 : (value > 32 ? 32 : value));
     else return ctx->fail(PTB_ERR_INVALID, "unknown option " + n);
     return PTB_OK;
 }

@@ -1479,7 +1479,16 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     // most slots are live the groups simply share the device; once few paths remain — every launch then lasts as long as the
     // slowest ray in it, a chain of dependent loads, whatever the number of rays — the G chains overlap instead of following one
     // another.  Per-launch profiling (CUDA events between consecutive launches of one stream) needs a single group.
-    const int G = prof ? 1 : std::max(1, std::min<int>(std::min(MAX_GROUPS, ctx->opt_wavefront_groups), (int)(n_slots / 4096u) + 1));
+    // automatic (-1): two rays per lane when the scene's trees are large enough for the stages of a warp to diverge and for a ray to live
+    // long enough to repay its record set-up (measured: C3, 519 wide nodes, + 6.4 % per frame, C4, 1.03 M nodes, + 5.5 %; C1, 332 nodes, - 3 %,
+    // C2, 8 nodes, - 3.5 % — the threshold sits between those, the option overrides it)
+    const int mr_want = ctx->opt_multiray < 0 ? (ctx->scene.wide.size() >= 384 ? 2 : 0) : ctx->opt_multiray;
+    const int mr_k = (!bin && threads == 128 && (mr_want == 2 || mr_want == 3)) ? mr_want : 0;
+    // wavefront groups and the refill threshold of the one-ray kernels: by default (< 0) 1 group / 4 lanes with the multiray kernels, 2 / 8
+    // without (sweeps: profiles/r3g_*, r3h_*: C3 256.5 -> 252.6 ms, C4 172.4 -> 170.3; C2 keeps 2 / 8: 162.3 against 167.5 with one group)
+    const int groups_want = ctx->opt_wavefront_groups < 0 ? (mr_k ? 1 : 2) : ctx->opt_wavefront_groups;
+    const int refill_want = ctx->opt_refill_below < 0 ? (mr_k ? 4 : 8) : ctx->opt_refill_below;
+    const int G = prof ? 1 : std::max(1, std::min<int>(std::min(MAX_GROUPS, groups_want), (int)(n_slots / 4096u) + 1));
     while ((int)rs.group_streams.size() < G - 1)
     {
         cudaStream_t s2;
@@ -1608,11 +1617,6 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
 
     // multiray kernels (option multiray = 2 / 3 rays per lane, multiray.cuh): dynamic shared memory for the ray records, as many resident
     // blocks per SM as fit (or mr_blocks)
-    // automatic (-1): two rays per lane when the scene's trees are large enough for the stages of a warp to diverge and for a ray to live
-    // long enough to repay its record set-up (measured: C3, 519 wide nodes, + 6.4 % per frame, C4, 1.03 M nodes, + 5.5 %; C1, 332 nodes, - 3 %,
-    // C2, 8 nodes, - 3.5 % — the threshold sits between those, the option overrides it)
-    const int mr_want = ctx->opt_multiray < 0 ? (ctx->scene.wide.size() >= 384 ? 2 : 0) : ctx->opt_multiray;
-    const int mr_k = (!bin && threads == 128 && (mr_want == 2 || mr_want == 3)) ? mr_want : 0;
     MrOpts mro = ctx->opt_mr;
     if (mro.free_quorum <= 0) mro.free_quorum = 24;
     const size_t mr_es = (size_t)mr_k * (MR_JOB + MrExtendJob::JOBW) * 128 * sizeof(uint32_t), mr_ns = (size_t)mr_k * (MR_JOB + MrNeeJob::JOBW) * 128 * sizeof(uint32_t);
@@ -1658,7 +1662,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     };
     for (int g = 0; g < G; ++g) gr[g].bound = gr[g].Q.npix;
     auto launch_path = [&](int g, uint32_t it) -> int {
-        const int pg = ctx->sm_count * ctx->opt_path_blocks, fq = ctx->opt_finish_quorum, rb = ctx->opt_refill_below, nq = ctx->opt_node_quorum;
+        const int pg = ctx->sm_count * ctx->opt_path_blocks, fq = ctx->opt_finish_quorum, rb = refill_want, nq = ctx->opt_node_quorum;
         switch (ctx->opt_path_blocks)
         {
         case 4: k_path<4><<<pg, threads, 0, gr[g].st>>>(V, gr[g].Q, it, rb, nq, fq); break;
@@ -1678,7 +1682,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         cudaStream_t gs = R.st;
         const uint32_t it = R.it;
         const bool dense = R.dense;
-        const int rb = ctx->opt_refill_below, rbn = ctx->opt_nee_refill_below, nq = ctx->opt_node_quorum;
+        const int rb = refill_want, rbn = ctx->opt_nee_refill_below, nq = ctx->opt_node_quorum;
         // thin iterations: k_nee of iteration it on its own stream, beside part 1 (continuing slots) of iteration it + 1's k_extend
         const bool ov = overlap_on && R.bound < ov_below && !(mr_k && R.bound >= mr_min);
         cudaStream_t ns = overlap_on ? rs.nee_streams[g] : gs;
