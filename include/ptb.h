@@ -244,6 +244,10 @@ int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, floa
  *   tile_pixels       1 (default): path slots are laid over the frame in tiles of 8 x 4 pixels, so that the 32 rays of a warp cover a compact
  *                     patch of the image instead of a 32 x 1 line (frames whose width divides by 8 and height by 4; same results bit for
  *                     bit, 1 - 1.5 % per frame); 0: row-major
+ *   tile_lists        camera rays start from their tile's list of TLAS leaves instead of the TLAS root: once per ptb_render one thread per
+ *                     8 x 4 pixel tile walks the world TLAS with the tile's frustum and lists the instances its rays can reach, nearest
+ *                     first (csrc/render.cu: k_tile_lists; needs tile_pixels).  1, 0, < 0 (default) = scenes of >= 64 instances.  Same
+ *                     results but for equal hits in different instances (visit order)
  *   nee_overlap       thin iterations (fewer live slots than this many per lane of the one-ray grid; 0 never = default, < 0 always): k_nee
  *                     of iteration i runs on a stream of its own beside the continuing slots' part of iteration i + 1's k_extend — a
  *                     continuing slot's next ray does not depend on its pending direct-light rays (same results; measured without gain: the thin iterations are issue-bound work on hard rays)

@@ -154,6 +154,10 @@ struct SceneDev
     uint32_t n_volumes;
     uint32_t env_w, env_h;
     float light_max;             // LightSampler::max
+    // per 8 x 4 pixel tile of the frame (render.cu: k_tile_lists): the TLAS leaves a camera ray of the tile can reach, nearest first —
+    // TILE_LIST_STRIDE uint2 per tile: [0] = (count | TILE_LIST_NONE, 0), then (leaf-header index, lower bound of the entry distance)
+    const uint2* tile_lists;
 };
+constexpr uint32_t TILE_LIST_STRIDE = 16, TILE_LIST_NONE = 0xffffffffu;
 
 }  // namespace ptb

@@ -18,7 +18,7 @@
 
 namespace ptb {
 
-template <int MODE, class Job, bool GATED = false, int SSTACK = 0>
+template <int MODE, class Job, bool GATED = false, int SSTACK = 0, bool LIST = false>
 __device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, uint32_t* cursor, uint32_t total, int refill_below, int node_quorum, int finish_quorum = 33)
 {
     // traversal stack: local memory, or (SSTACK > 0, blocks of 128 threads) its first SSTACK entries in shared memory
@@ -83,7 +83,7 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& S, Job& job, ui
         unsigned done = 0u;
         do
         {
-            if (state == 1 && !wide_step_pop(tr, S, stack)) state = 2;
+            if (state == 1 && !wide_step_pop<LIST>(tr, S, stack)) state = 2;
             // the node stage runs when at least node_quorum lanes want it, or when no lane has leaf/triangle work left
             const unsigned wn = __ballot_sync(FULL, state == 1 && wide_wants_node(tr));
             const unsigned wl = __ballot_sync(FULL, state == 1 && wide_has_leaf_work(tr));

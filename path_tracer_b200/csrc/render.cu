@@ -74,6 +74,7 @@ struct RenderState
     DBuf<ProbeRec> probe;
     DBuf<uint32_t> id, q_cont0, q_cont1, q_term0, q_term1, q_mat, q_nee, slot_state, q_grp0, q_grp1;
     DBuf<unsigned long long> volset;
+    DBuf<uint2> tile_lists;  // per 8 x 4 pixel tile: the TLAS leaves its camera rays can reach (k_tile_lists)
     DBuf<WfCounters> counters;
     float4* accum = nullptr;  // bound or own
     uint32_t* h_flags = nullptr;  // pinned, MAX_GROUPS x POLL_RING x 4 (n_cont, n_term, n_nee, n_grp of every iteration of every group)
@@ -183,6 +184,100 @@ __global__ void __launch_bounds__(256) k_combine(RenderView V, float4* accum_px,
     }
 }
 
+// ---- candidate lists of the camera rays, one per 8 x 4 pixel tile ------------------------------------------------------------------
+// Camera rays are half of the closest-hit rays of an instanced scene (C3: 132.7 M of 270 M per step), and every one of them walks the
+// TLAS from its root (3.7 node tests of 7.8) although the 32 rays of a warp leave one point through one small patch of the image.  Per
+// render call, one thread per tile walks the world TLAS once with the tile's frustum — the four rays through the corners of its pixel
+// area, jitter included — and lists the TLAS leaves (instances) the frustum touches, nearest first, each with a lower bound of the
+// distance at which a ray can enter it.  A regenerated slot's ray then starts from its tile's list (wide_begin_list, traverse.h)
+// instead of the TLAS root.  The tests here only cull, with margins; every listed leaf is still entered through its exact box test.
+constexpr uint32_t TILE_LIST_CAP = TILE_LIST_STRIDE - 1;
+__global__ void __launch_bounds__(128) k_tile_lists(RenderView V, uint2* lists, uint32_t n_tiles)
+{
+    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile >= n_tiles) return;
+    const float x0 = (float)((tile % V.tiles_x) * 8u), y0 = (float)((tile / V.tiles_x) * 4u);
+    // pixel area of the tile with the jitter range (-0.5, 0.5) and a margin, as raygen's (u, v) (regen_slot)
+    const float u0 = (x0 - 0.52f) / (float)V.W, u1 = (x0 + 7.52f) / (float)V.W, v0 = (y0 - 0.52f) / (float)V.H, v1 = (y0 + 3.52f) / (float)V.H;
+    V3 e, c[4];
+    camera_ray(V.cam, u0, v0, &e, &c[0]);
+    camera_ray(V.cam, u1, v0, &e, &c[1]);
+    camera_ray(V.cam, u1, v1, &e, &c[2]);
+    camera_ray(V.cam, u0, v1, &e, &c[3]);
+    // side planes through the eye: normal = cross of two neighbouring corner rays, turned towards the opposite corner
+    V3 n[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+    {
+        V3 m = crossf(c[k], c[(k + 1) & 3]);
+        m = m * (1.0f / sqrtf(dot(m, m)));
+        if (dot(m, c[(k + 2) & 3]) < 0.0f) m = -m;
+        n[k] = m;
+    }
+    // 1: the box may hold a point of the frustum; *dmin: lower bound of the distance from the eye to the box
+    auto touches = [&](V3 lo, V3 hi, float* dmin) -> bool {
+        const V3 a = lo - e, b = hi - e;
+        const float R = fmaxf(fmaxf(fmaxf(fabsf(a.x), fabsf(b.x)), fmaxf(fabsf(a.y), fabsf(b.y))), fmaxf(fabsf(a.z), fabsf(b.z)));
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+        {
+            const float s = fmaxf(n[k].x * a.x, n[k].x * b.x) + fmaxf(n[k].y * a.y, n[k].y * b.y) + fmaxf(n[k].z * a.z, n[k].z * b.z);
+            if (s < -1e-4f * R) return false;  // every corner of the box is outside this side plane
+        }
+        const float dx = fmaxf(fmaxf(a.x, -b.x), 0.0f), dy = fmaxf(fmaxf(a.y, -b.y), 0.0f), dz = fmaxf(fmaxf(a.z, -b.z), 0.0f);
+        *dmin = fmaxf(sqrtf(dx * dx + dy * dy + dz * dz) * 0.9999f - 1e-4f * R, 0.0f);
+        return true;
+    };
+    uint32_t stack[48];
+    int sp = 0;
+    stack[sp++] = V.S.tlas[0].wide_root;
+    uint2 best[TILE_LIST_CAP];
+    uint32_t cnt = 0;
+    bool overflow = false;
+    while (sp > 0 && !overflow)
+    {
+        const uint4* np = V.S.wide + (size_t)stack[--sp] * 5;
+        const uint4 q0 = np[0], q1 = np[1], q2 = np[2], q3 = np[3], q4 = np[4];
+        const V3 p = ex::v3(__uint_as_float(q0.x), __uint_as_float(q0.y), __uint_as_float(q0.z));
+        const V3 sc = ex::v3(__uint_as_float((q0.w & 0xffu) << 23), __uint_as_float(((q0.w >> 8) & 0xffu) << 23), __uint_as_float(((q0.w >> 16) & 0xffu) << 23));
+        const uint32_t imask = q0.w >> 24, lmask = q1.z & 0xffu;
+        const uint32_t lo_w[6] = {q2.x, q2.y, q2.z, q2.w, q3.x, q3.y}, hi_w[6] = {q3.z, q3.w, q4.x, q4.y, q4.z, q4.w};  // x, y, z planes of the slots 0-3 | 4-7
+        for (uint32_t s = 0; s < 8u; ++s)
+        {
+            if (!(((imask | lmask) >> s) & 1u)) continue;
+            float dmin;
+            if ((lmask >> s) & 1u)
+            {
+                const uint32_t hidx = q1.y + (uint32_t)__popc(lmask & ((1u << s) - 1u));
+                const float4* lp = V.S.leaf_headers + (size_t)hidx * LEAF_F4;
+                const float4 h0 = lp[0], h1 = lp[1];
+                if (!touches(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), &dmin)) continue;
+                if (cnt == TILE_LIST_CAP) { overflow = true; break; }
+                // insertion by distance, nearest first
+                uint32_t i = cnt++;
+                for (; i > 0 && __uint_as_float(best[i - 1].y) > dmin; --i) best[i] = best[i - 1];
+                best[i] = make_uint2(hidx, __float_as_uint(dmin));
+            }
+            else
+            {
+                const uint32_t sh = (s & 3u) * 8u, w = s >> 2;
+                // quantised child box (a superset of the child's own), one more step of slack on either side
+                const V3 lo = ex::v3(p.x + ((float)((lo_w[0 + w] >> sh) & 0xffu) - 1.0f) * sc.x, p.y + ((float)((lo_w[2 + w] >> sh) & 0xffu) - 1.0f) * sc.y,
+                                     p.z + ((float)((lo_w[4 + w] >> sh) & 0xffu) - 1.0f) * sc.z);
+                const V3 hi = ex::v3(p.x + ((float)((hi_w[0 + w] >> sh) & 0xffu) + 1.0f) * sc.x, p.y + ((float)((hi_w[2 + w] >> sh) & 0xffu) + 1.0f) * sc.y,
+                                     p.z + ((float)((hi_w[4 + w] >> sh) & 0xffu) + 1.0f) * sc.z);
+                if (!touches(lo, hi, &dmin)) continue;
+                if (sp == 48) { overflow = true; break; }
+                stack[sp++] = q1.x + (uint32_t)__popc(imask & ((1u << s) - 1u));
+            }
+        }
+    }
+    uint2* out = lists + (size_t)tile * TILE_LIST_STRIDE;
+    out[0] = make_uint2(overflow ? TILE_LIST_NONE : cnt, 0u);
+    if (!overflow)
+        for (uint32_t i = 0; i < cnt; ++i) out[1 + i] = best[i];
+}
+
 // ---- extend: dynamic-fetch persistent kernel over the 8-wide layout --------------------------------------------------------
 struct ExtendJob
 {
@@ -223,6 +318,17 @@ struct ExtendJob
                 ++settled;
             }
             Q.state[slot] = WF_NEXT;  // live: a ray is being traced for it this iteration
+            if (V.S.tile_lists)
+            {
+                // a camera ray: from its tile's list of TLAS leaves instead of the TLAS root (k_tile_lists)
+                const uint32_t first = ((slot % V.npix) >> 5) * TILE_LIST_STRIDE;
+                const uint32_t n = V.S.tile_lists[first].x;
+                if (n != TILE_LIST_NONE)
+                {
+                    wide_begin_list(tr, V.S, o, d, ex::inf(), first + 1u, first + 1u + n);
+                    return true;
+                }
+            }
         }
         wide_begin(tr, V.S, 0, o, d, ex::inf(), false);
         return true;
@@ -270,7 +376,8 @@ __global__ void __launch_bounds__(128, MB) k_extend(RenderView V, Queues Q, uint
     }
     ExtendJob job{V, Q, S, it & 1u, n_cont, n_term, sort};
     if (part == 2) job.idx0 = n_cont;
-    persistent_trace<0, ExtendJob, false, SSTACK>(V.S, job, part == 2 ? &S.cur_regen : &S.cur_extend, part == 2 ? n_term : (part == 1 ? n_cont : n_cont + n_term), refill_below, node_quorum);
+    if (V.S.tile_lists) persistent_trace<0, ExtendJob, false, SSTACK, true>(V.S, job, part == 2 ? &S.cur_regen : &S.cur_extend, part == 2 ? n_term : (part == 1 ? n_cont : n_cont + n_term), refill_below, node_quorum);
+    else persistent_trace<0, ExtendJob, false, SSTACK>(V.S, job, part == 2 ? &S.cur_regen : &S.cur_extend, part == 2 ? n_term : (part == 1 ? n_cont : n_cont + n_term), refill_below, node_quorum);
     const unsigned long long p = warp_sum(job.paths), q = warp_sum(job.settled);
     if ((threadIdx.x & 31u) == 0u && p) atomicAdd(&Q.c->stat_paths, p);
     if ((threadIdx.x & 31u) == 0u && q) atomicAdd(&Q.c->stat_settled, q);  // primary rays settled in start() without a traversal: counted apart
@@ -1457,6 +1564,14 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     V.W = rs.W; V.H = rs.H;
     V.npix = rs.npix;
     V.tiles_x = (ctx->opt_tile_pixels && rs.W % 8u == 0u && rs.H % 4u == 0u) ? rs.W / 8u : 0u;
+    // camera rays from per-tile lists of TLAS leaves (k_tile_lists): scenes of many instances (automatic: >= 64), wide kernels, tiled slots
+    const uint32_t n_tiles = V.tiles_x * (rs.H / 4u);
+    const bool use_tile_lists = V.tiles_x > 0u && !ctx->opt_extend_kernel && (ctx->opt_tile_lists < 0 ? ctx->scene.inst_rows.size() >= 64u : ctx->opt_tile_lists != 0);
+    if (use_tile_lists)
+    {
+        PTB_CUDA(ctx, rs.tile_lists.resize((size_t)n_tiles * TILE_LIST_STRIDE));
+        V.S.tile_lists = rs.tile_lists.p;
+    }
     V.K = K;
     V.sample_begin = sample_begin; V.sample_count = sample_count;
     V.seed = seed;
@@ -1581,6 +1696,11 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
 
     PTB_CUDA(ctx, cudaEventRecord(rs.ev_begin, st));
     PTB_CUDA(ctx, mark(-1));
+    if (use_tile_lists)
+    {
+        k_tile_lists<<<(n_tiles + 127u) / 128u, 128, 0, st>>>(V, rs.tile_lists.p, n_tiles);
+        rs.launches += 1;
+    }
     for (int g = 0; g < G; ++g) k_init<<<(gr[g].Q.npix + threads - 1) / threads, threads, 0, st>>>(V, gr[g].Q, rs.id.p);
     PTB_CUDA(ctx, mark(1));
     rs.launches += G;

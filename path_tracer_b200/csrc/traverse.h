@@ -234,6 +234,7 @@ struct WideTrav
     float hit_ud, hit_vd, hit_det;  // winner's undivided barycentrics (u = ud / det, v = vd / det: wide_hit_u / wide_hit_v)
     uint32_t hit_slot, hit_inst;  // hit_inst == TRAV_NONE: nothing found yet
     uint32_t any;       // any-hit query (TLAS::any_intersect) — used when the step is instantiated with MODE == 2
+    uint32_t cand, cand_end;  // LIST traversals (camera rays of a tile, wide_begin_list): next / end entry of the tile's list in S.tile_lists
 };
 
 // Conservative pre-test against the widened world bounds of TLAS `which`: false only if no point of the ray (t >= 0) lies in
@@ -287,6 +288,17 @@ PTB_HD void wide_begin(WideTrav& s, const SceneDev& S, int which, V3 o, V3 d, fl
     s.hit_slot = 0;
     s.hit_inst = TRAV_NONE;
     s.any = any ? 1u : 0u;
+    s.cand = s.cand_end = 0u;
+}
+// closest hit over a precomputed list of TLAS leaves instead of the TLAS itself: the list holds every leaf the ray can reach (a superset,
+// nearest first, each with a lower bound of its entry distance), the leaves are entered through the same exact box test, so the nearest
+// hit is the one the TLAS walk finds (equal hits in different instances may resolve differently: the visit order differs)
+PTB_HD void wide_begin_list(WideTrav& s, const SceneDev& S, V3 o, V3 d, float t_max, uint32_t first, uint32_t end)
+{
+    wide_begin(s, S, 0, o, d, t_max, false);
+    s.node = TRAV_NONE;
+    s.cand = first;
+    s.cand_end = end;
 }
 
 PTB_HD int hi_bit(uint32_t m)
@@ -317,7 +329,7 @@ PTB_HD uint32_t popc32(uint32_t m)
 // MODE 0: closest hit, 1: any hit, 2: s.any decides at run time.  Returns false when the traversal is complete
 // (closest: s.hit_inst != TRAV_NONE tells whether something was hit; any: s.hit_inst != TRAV_NONE == occluded).
 // wide_step_pop: stage P.  Returns false when the traversal is complete (stack empty, nothing pending).
-template <class Stack>
+template <bool LIST = false, class Stack>
 PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, Stack stack)
 {
     // ---- P: nothing pending -> next node from the current group, or pop ----------------------------------------------
@@ -334,8 +346,16 @@ PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, Stack stack)
                 s.ray.idq = ex::v3(finite_recip_of(s.invw.x), finite_recip_of(s.invw.y), finite_recip_of(s.invw.z));
                 s.ray.oi = s.oiw;
             }
-            if (s.sp == 0) return false;
-            const uint2 e = stk_get(stack, --s.sp);
+            uint2 e;
+            if (s.sp == 0)
+            {
+                if (!LIST || s.cand >= s.cand_end) return false;
+                const uint2 c = S.tile_lists[s.cand++];
+                if (ex::from_bits(c.y) > s.t_max) { s.cand = s.cand_end; return false; }  // nearest first: nothing further can be nearer than the hit
+                e.x = c.x;
+                e.y = 0x80000000u;
+            }
+            else e = stk_get(stack, --s.sp);
             if (e.y & 0x80000000u)
             {
                 // TLAS leaf (tlas.rs:88-100 / :132-139): exact leaf box with the current t_max, then Ray::transform

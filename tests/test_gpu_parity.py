@@ -410,6 +410,33 @@ def test_multiray_render_equals_lane(ptb, scenes, name, spp, W, H):
         assert all(np.array_equal(a, b) for a, b in zip(ref[:3], v[:3])), f"multiray={k}: outputs differ"
 
 
+@pytest.mark.parametrize("name,spp,W,H", [("c3_small", 5, 96, 56), ("c3_small", 4, 32, 16), ("c4_small", 4, 96, 56), ("c2", 6, 96, 56), ("materials", 6, 64, 36)])
+def test_tile_lists_equal_tlas_walk(ptb, scenes, name, spp, W, H):
+    """Camera rays that start from their tile's list of TLAS leaves (k_tile_lists: one frustum walk of the TLAS per 8 x 4 pixel tile and
+    render call) against camera rays that walk the TLAS from its root: the lists only cull, with margins, and every listed leaf is entered
+    through its exact box test, so the frames, the aux outputs and the ray counters are identical — also where a tile sees more leaves
+    than a list holds (32 x 16 pixels on the whole scene: those tiles fall back to the TLAS walk) and with the row-major slot layout
+    (tile_pixels = 0: no lists)."""
+    sd = _scene(scenes, name)
+    out = {}
+    for tl, tp in ((0, 1), (1, 1), (1, 0)):
+        ctx = ptb.Context(0)
+        ctx.upload(sd)
+        ctx.set_option("tile_lists", tl)
+        ctx.set_option("tile_pixels", tp)
+        ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
+        ctx.frame_begin(W, H)
+        ctx.reset_counters()
+        ctx.render(0, spp, seed=31, max_bounces=sd.max_bounces)
+        pos, ids = ctx.read_aux()
+        c = ctx.counters()
+        out[(tl, tp)] = (bits(ctx.read_accum()), bits(pos), ids.copy(), (c["extend"], c["settled"], c["shadow"], c["probe"], c["paths"]))
+    ref = out[(0, 1)]
+    for k, v in out.items():
+        assert ref[3] == v[3], f"tile_lists, tile_pixels = {k}: ray counters differ: {ref[3]} vs {v[3]}"
+        assert all(np.array_equal(a, b) for a, b in zip(ref[:3], v[:3])), f"tile_lists, tile_pixels = {k}: outputs differ"
+
+
 def _group_render(group, sd, W, H, begin, count, seed):
     group.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
     group.frame_begin(W, H)
