@@ -16,6 +16,7 @@
 // slot to completion, one thread per slot, instead of thousands of near-empty iterations.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 
 #include "camera_host.h"
@@ -313,7 +314,9 @@ struct ExtendJob
                 // constant background the whole path is that miss (integrator.rs:254-269 at b == 0: radiance = background * 1).  Settle
                 // it here and start the slot's next sample at once; background pixels then never occupy the later kernels.
                 // (Slot-ordered shading only: the queue shade kernel expects every traced slot in one of its queues.)
-                if (sort >= 0 || V.S.env != nullptr || tlas_may_hit(V.S, 0, o, d)) break;
+                if (sort >= 0 || V.S.env != nullptr) break;
+                // ... and so is a camera ray whose tile's list of TLAS leaves is empty (k_tile_lists: no instance box touches the tile's frustum)
+                if (tlas_may_hit(V.S, 0, o, d) && !(V.S.tile_lists && V.S.tile_lists[((slot % V.npix) >> 5) * TILE_LIST_STRIDE].x == 0u)) break;
                 V.path[slot].radiance = f4(0.006f, 0.006f, 0.006f, 0.0f);
                 ++settled;
             }
@@ -1700,6 +1703,24 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     {
         k_tile_lists<<<(n_tiles + 127u) / 128u, 128, 0, st>>>(V, rs.tile_lists.p, n_tiles);
         rs.launches += 1;
+        if (std::getenv("PTB_TILE_STATS"))
+        {
+            // development aid: histogram of the list lengths (stderr)
+            std::vector<uint2> h((size_t)n_tiles * TILE_LIST_STRIDE);
+            PTB_CUDA(ctx, cudaMemcpyAsync(h.data(), rs.tile_lists.p, h.size() * sizeof(uint2), cudaMemcpyDeviceToHost, st));
+            PTB_CUDA(ctx, cudaStreamSynchronize(st));
+            uint32_t hist[TILE_LIST_STRIDE + 1] = {0};
+            unsigned long long sum = 0;
+            for (uint32_t t = 0; t < n_tiles; ++t)
+            {
+                const uint32_t n = h[(size_t)t * TILE_LIST_STRIDE].x;
+                hist[n == TILE_LIST_NONE ? TILE_LIST_STRIDE : n] += 1;
+                if (n != TILE_LIST_NONE) sum += n;
+            }
+            std::fprintf(stderr, "tile lists: %u tiles, mean length %.2f, overflow %u;", n_tiles, (double)sum / n_tiles, hist[TILE_LIST_STRIDE]);
+            for (uint32_t k = 0; k < TILE_LIST_STRIDE; ++k) std::fprintf(stderr, " %u:%u", k, hist[k]);
+            std::fprintf(stderr, "\n");
+        }
     }
     for (int g = 0; g < G; ++g) k_init<<<(gr[g].Q.npix + threads - 1) / threads, threads, 0, st>>>(V, gr[g].Q, rs.id.p);
     PTB_CUDA(ctx, mark(1));
