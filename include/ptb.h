@@ -240,7 +240,9 @@ int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, floa
  *                     of >= 384 wide nodes.  Same results bit for bit.  mr_qn / mr_ql / mr_qi (12 / 8 / 8): lanes that must hold a ray
  *                     waiting for the node / leaf / instance stage before a warp runs it; mr_free_quorum (24): finished or idle ray
  *                     slots of a warp that trigger a refill; mr_blocks: resident blocks per SM (0 = what fits); mr_min_per_lane (16):
- *                     iterations with fewer live slots per lane of the one-ray grid run the one-ray kernels
+ *                     iterations with fewer live slots per lane of the one-ray grid run the one-ray kernels; mr_split (1): k_extend in two
+ *                     launches, continuing slots two rays per lane, slots to regenerate (camera rays) one per lane; regen_blocks (7): resident
+ *                     blocks per SM of that second launch (5..8)
  *   tile_pixels       1 (default): path slots are laid over the frame in tiles of 8 x 4 pixels, so that the 32 rays of a warp cover a compact
  *                     patch of the image instead of a 32 x 1 line (frames whose width divides by 8 and height by 4; same results bit for
  *                     bit, 1 - 1.5 % per frame); 0: row-major

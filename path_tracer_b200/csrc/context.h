@@ -95,6 +95,7 @@ struct ptb_context
     int opt_tile_lists = -1;      // camera rays start from their tile's list of TLAS leaves (k_tile_lists): 1, 0, < 0 = scenes of >= 64 instances
     int opt_tile_pixels = 1;      // slots laid over the frame in 8 x 4 pixel tiles (a warp's 32 rays cover a compact patch) instead of row-major lines
     int opt_nee_overlap = 0;      // live slots per lane of the one-ray grid below which k_nee runs beside the next iteration's k_extend (0 never, < 0 always)
+    int opt_regen_blocks = 7;     // resident blocks per SM (= register cap) of the regeneration part of a two-part k_extend launch (5..8)
     int opt_mr_split = 1;         // with the multiray kernels: continuing slots (bounce rays) two per lane, regenerated slots (primary rays) one per lane, two launches
     int opt_mr_min_per_lane = 16; // multiray kernels only while the live slots are at least this many per lane of the one-ray grid
     MrOpts opt_mr;                // multiray kernels (mr_free_quorum, mr_qn, mr_ql, mr_qi, mr_blocks)

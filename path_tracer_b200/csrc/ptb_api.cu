@@ -436,6 +436,7 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "tile_lists") ctx->opt_tile_lists = value;
     else if (n == "tile_pixels") ctx->opt_tile_pixels = value ? 1 : 0;
     else if (n == "nee_overlap") ctx->opt_nee_overlap = value;
+    else if (n == "regen_blocks") ctx->opt_regen_blocks = value;
     else if (n == "mr_split") ctx->opt_mr_split = value ? 1 : 0;
     else if (n == "mr_min_per_lane") ctx->opt_mr_min_per_lane = value;
     else if (n == "mr_free_quorum") ctx->opt_mr.free_quorum = value;

@@ -1852,7 +1852,13 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
             else k_extend_mr<2><<<eg, 128, mr_es, gs>>>(V, Q, it, so, mro, part);
             if (part)
             {
-                k_extend<7><<<sized_grid(7, R.bound), threads, 0, gs>>>(V, Q, it, so, rb, nq, 2);
+                switch (ctx->opt_regen_blocks)
+                {
+                case 5: k_extend<5><<<sized_grid(5, R.bound), threads, 0, gs>>>(V, Q, it, so, rb, nq, 2); break;
+                case 6: k_extend<6><<<sized_grid(6, R.bound), threads, 0, gs>>>(V, Q, it, so, rb, nq, 2); break;
+                case 8: k_extend<8><<<sized_grid(8, R.bound), threads, 0, gs>>>(V, Q, it, so, rb, nq, 2); break;
+                default: k_extend<7><<<sized_grid(7, R.bound), threads, 0, gs>>>(V, Q, it, so, rb, nq, 2); break;
+                }
                 rs.launches += 1;
             }
         }
