@@ -1,0 +1,8 @@
+T=r3s
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${T}_pytest.log
+tail -3 gpurun_out/${T}_pytest.log
+python __graft_entry__.py smoke > gpurun_out/${T}_smoke.log 2>&1; tail -1 gpurun_out/${T}_smoke.log
+python bench.py --impl reference > gpurun_out/${T}_bench_reference_arm.json 2> gpurun_out/${T}_bench.err
+python bench.py > gpurun_out/${T}_bench.json 2>> gpurun_out/${T}_bench.err
+cut -c1-200 gpurun_out/${T}_bench.json
