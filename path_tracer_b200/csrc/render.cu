@@ -315,8 +315,9 @@ struct ExtendJob
                 // it here and start the slot's next sample at once; background pixels then never occupy the later kernels.
                 // (Slot-ordered shading only: the queue shade kernel expects every traced slot in one of its queues.)
                 if (sort >= 0 || V.S.env != nullptr) break;
-                // ... and so is a camera ray whose tile's list of TLAS leaves is empty (k_tile_lists: no instance box touches the tile's frustum)
-                if (tlas_may_hit(V.S, 0, o, d) && !(V.S.tile_lists && V.S.tile_lists[((slot % V.npix) >> 5) * TILE_LIST_STRIDE].x == 0u)) break;
+                // ... and so is a camera ray whose tile's list of TLAS leaves is empty (k_tile_lists: no instance box touches the tile's frustum);
+                // option tile_settle, off by default: such a ray then leaves the traced count, which the roofline figure is stated on
+                if (tlas_may_hit(V.S, 0, o, d) && !(V.tile_settle && V.S.tile_lists && V.S.tile_lists[((slot % V.npix) >> 5) * TILE_LIST_STRIDE].x == 0u)) break;
                 V.path[slot].radiance = f4(0.006f, 0.006f, 0.006f, 0.0f);
                 ++settled;
             }
@@ -1574,6 +1575,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
     {
         PTB_CUDA(ctx, rs.tile_lists.resize((size_t)n_tiles * TILE_LIST_STRIDE));
         V.S.tile_lists = rs.tile_lists.p;
+        V.tile_settle = ctx->opt_tile_settle ? 1u : 0u;
     }
     V.K = K;
     V.sample_begin = sample_begin; V.sample_count = sample_count;

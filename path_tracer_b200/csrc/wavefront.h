@@ -58,6 +58,7 @@ struct RenderView
     uint32_t W, H;
     uint32_t npix;           // W * H
     uint32_t K;              // slots per pixel: slot = k * npix + j renders the samples k, k + K, k + 2K, ... of pixel slot_pixel(j)
+    uint32_t tile_settle;    // camera rays of a tile whose list of TLAS leaves is empty are settled in the regeneration loop (option tile_settle)
     uint32_t tiles_x;        // > 0: slots are laid over the frame in tiles of 8 x 4 pixels (W / 8 tiles per row), so that the 32 rays of a warp
                              // cover a compact patch of the image instead of a 32 x 1 line; 0: j = pixel (frame sizes that do not divide)
     uint32_t sample_begin, sample_count;
