@@ -192,91 +192,10 @@ __global__ void __launch_bounds__(256) k_combine(RenderView V, float4* accum_px,
 // area, jitter included — and lists the TLAS leaves (instances) the frustum touches, nearest first, each with a lower bound of the
 // distance at which a ray can enter it.  A regenerated slot's ray then starts from its tile's list (wide_begin_list, traverse.h)
 // instead of the TLAS root.  The tests here only cull, with margins; every listed leaf is still entered through its exact box test.
-constexpr uint32_t TILE_LIST_CAP = TILE_LIST_STRIDE - 1;
 __global__ void __launch_bounds__(128) k_tile_lists(RenderView V, uint2* lists, uint32_t n_tiles)
 {
     const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tile >= n_tiles) return;
-    const float x0 = (float)((tile % V.tiles_x) * 8u), y0 = (float)((tile / V.tiles_x) * 4u);
-    // pixel area of the tile with the jitter range (-0.5, 0.5) and a margin, as raygen's (u, v) (regen_slot)
-    const float u0 = (x0 - 0.52f) / (float)V.W, u1 = (x0 + 7.52f) / (float)V.W, v0 = (y0 - 0.52f) / (float)V.H, v1 = (y0 + 3.52f) / (float)V.H;
-    V3 e, c[4];
-    camera_ray(V.cam, u0, v0, &e, &c[0]);
-    camera_ray(V.cam, u1, v0, &e, &c[1]);
-    camera_ray(V.cam, u1, v1, &e, &c[2]);
-    camera_ray(V.cam, u0, v1, &e, &c[3]);
-    // side planes through the eye: normal = cross of two neighbouring corner rays, turned towards the opposite corner
-    V3 n[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-    {
-        V3 m = crossf(c[k], c[(k + 1) & 3]);
-        m = m * (1.0f / sqrtf(dot(m, m)));
-        if (dot(m, c[(k + 2) & 3]) < 0.0f) m = -m;
-        n[k] = m;
-    }
-    // 1: the box may hold a point of the frustum; *dmin: lower bound of the distance from the eye to the box
-    auto touches = [&](V3 lo, V3 hi, float* dmin) -> bool {
-        const V3 a = lo - e, b = hi - e;
-        const float R = fmaxf(fmaxf(fmaxf(fabsf(a.x), fabsf(b.x)), fmaxf(fabsf(a.y), fabsf(b.y))), fmaxf(fabsf(a.z), fabsf(b.z)));
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-        {
-            const float s = fmaxf(n[k].x * a.x, n[k].x * b.x) + fmaxf(n[k].y * a.y, n[k].y * b.y) + fmaxf(n[k].z * a.z, n[k].z * b.z);
-            if (s < -1e-4f * R) return false;  // every corner of the box is outside this side plane
-        }
-        const float dx = fmaxf(fmaxf(a.x, -b.x), 0.0f), dy = fmaxf(fmaxf(a.y, -b.y), 0.0f), dz = fmaxf(fmaxf(a.z, -b.z), 0.0f);
-        *dmin = fmaxf(sqrtf(dx * dx + dy * dy + dz * dz) * 0.9999f - 1e-4f * R, 0.0f);
-        return true;
-    };
-    uint32_t stack[48];
-    int sp = 0;
-    stack[sp++] = V.S.tlas[0].wide_root;
-    uint2 best[TILE_LIST_CAP];
-    uint32_t cnt = 0;
-    bool overflow = false;
-    while (sp > 0 && !overflow)
-    {
-        const uint4* np = V.S.wide + (size_t)stack[--sp] * 5;
-        const uint4 q0 = np[0], q1 = np[1], q2 = np[2], q3 = np[3], q4 = np[4];
-        const V3 p = ex::v3(__uint_as_float(q0.x), __uint_as_float(q0.y), __uint_as_float(q0.z));
-        const V3 sc = ex::v3(__uint_as_float((q0.w & 0xffu) << 23), __uint_as_float(((q0.w >> 8) & 0xffu) << 23), __uint_as_float(((q0.w >> 16) & 0xffu) << 23));
-        const uint32_t imask = q0.w >> 24, lmask = q1.z & 0xffu;
-        const uint32_t lo_w[6] = {q2.x, q2.y, q2.z, q2.w, q3.x, q3.y}, hi_w[6] = {q3.z, q3.w, q4.x, q4.y, q4.z, q4.w};  // x, y, z planes of the slots 0-3 | 4-7
-        for (uint32_t s = 0; s < 8u; ++s)
-        {
-            if (!(((imask | lmask) >> s) & 1u)) continue;
-            float dmin;
-            if ((lmask >> s) & 1u)
-            {
-                const uint32_t hidx = q1.y + (uint32_t)__popc(lmask & ((1u << s) - 1u));
-                const float4* lp = V.S.leaf_headers + (size_t)hidx * LEAF_F4;
-                const float4 h0 = lp[0], h1 = lp[1];
-                if (!touches(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), &dmin)) continue;
-                if (cnt == TILE_LIST_CAP) { overflow = true; break; }
-                // insertion by distance, nearest first
-                uint32_t i = cnt++;
-                for (; i > 0 && __uint_as_float(best[i - 1].y) > dmin; --i) best[i] = best[i - 1];
-                best[i] = make_uint2(hidx, __float_as_uint(dmin));
-            }
-            else
-            {
-                const uint32_t sh = (s & 3u) * 8u, w = s >> 2;
-                // quantised child box (a superset of the child's own), one more step of slack on either side
-                const V3 lo = ex::v3(p.x + ((float)((lo_w[0 + w] >> sh) & 0xffu) - 1.0f) * sc.x, p.y + ((float)((lo_w[2 + w] >> sh) & 0xffu) - 1.0f) * sc.y,
-                                     p.z + ((float)((lo_w[4 + w] >> sh) & 0xffu) - 1.0f) * sc.z);
-                const V3 hi = ex::v3(p.x + ((float)((hi_w[0 + w] >> sh) & 0xffu) + 1.0f) * sc.x, p.y + ((float)((hi_w[2 + w] >> sh) & 0xffu) + 1.0f) * sc.y,
-                                     p.z + ((float)((hi_w[4 + w] >> sh) & 0xffu) + 1.0f) * sc.z);
-                if (!touches(lo, hi, &dmin)) continue;
-                if (sp == 48) { overflow = true; break; }
-                stack[sp++] = q1.x + (uint32_t)__popc(imask & ((1u << s) - 1u));
-            }
-        }
-    }
-    uint2* out = lists + (size_t)tile * TILE_LIST_STRIDE;
-    out[0] = make_uint2(overflow ? TILE_LIST_NONE : cnt, 0u);
-    if (!overflow)
-        for (uint32_t i = 0; i < cnt; ++i) out[1 + i] = best[i];
+    if (tile < n_tiles) tile_list_build(V, tile, lists + (size_t)tile * TILE_LIST_STRIDE);  // wavefront.h
 }
 
 // ---- extend: dynamic-fetch persistent kernel over the 8-wide layout --------------------------------------------------------

@@ -108,6 +108,94 @@ PTB_HD float4 f4(float x, float y, float z, float w)
     return r;
 }
 
+// ---- candidate list of one 8 x 4 pixel tile (k_tile_lists, render.cu; host-callable so that the culling can be tested on the CPU) -------------
+// Walks the world TLAS with the tile's frustum — the four rays through the corners of its pixel area, jitter and a margin included — and
+// writes the TLAS leaves the frustum touches, nearest first, each with a lower bound of the distance at which a ray can enter it.
+// out: TILE_LIST_STRIDE entries, [0] = (count | TILE_LIST_NONE when the tile sees more leaves than the list holds, 0).
+constexpr uint32_t TILE_LIST_CAP = TILE_LIST_STRIDE - 1;
+PTB_HD void tile_list_build(const RenderView& V, uint32_t tile, uint2* out)
+{
+    const float x0 = (float)((tile % V.tiles_x) * 8u), y0 = (float)((tile / V.tiles_x) * 4u);
+    // pixel area of the tile with the jitter range (-0.5, 0.5) and a margin, as raygen's (u, v) (regen_slot)
+    const float u0 = (x0 - 0.52f) / (float)V.W, u1 = (x0 + 7.52f) / (float)V.W, v0 = (y0 - 0.52f) / (float)V.H, v1 = (y0 + 3.52f) / (float)V.H;
+    V3 e, c[4];
+    camera_ray(V.cam, u0, v0, &e, &c[0]);
+    camera_ray(V.cam, u1, v0, &e, &c[1]);
+    camera_ray(V.cam, u1, v1, &e, &c[2]);
+    camera_ray(V.cam, u0, v1, &e, &c[3]);
+    // side planes through the eye: normal = cross of two neighbouring corner rays, turned towards the opposite corner
+    V3 n[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+    {
+        V3 m = crossf(c[k], c[(k + 1) & 3]);
+        m = m * (1.0f / sqrtf(dot(m, m)));
+        if (dot(m, c[(k + 2) & 3]) < 0.0f) m = -m;
+        n[k] = m;
+    }
+    // 1: the box may hold a point of the frustum; *dmin: lower bound of the distance from the eye to the box
+    auto touches = [&](V3 lo, V3 hi, float* dmin) -> bool {
+        const V3 a = lo - e, b = hi - e;
+        const float R = fmaxf(fmaxf(fmaxf(fabsf(a.x), fabsf(b.x)), fmaxf(fabsf(a.y), fabsf(b.y))), fmaxf(fabsf(a.z), fabsf(b.z)));
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+        {
+            const float s = fmaxf(n[k].x * a.x, n[k].x * b.x) + fmaxf(n[k].y * a.y, n[k].y * b.y) + fmaxf(n[k].z * a.z, n[k].z * b.z);
+            if (s < -1e-4f * R) return false;  // every corner of the box is outside this side plane
+        }
+        const float dx = fmaxf(fmaxf(a.x, -b.x), 0.0f), dy = fmaxf(fmaxf(a.y, -b.y), 0.0f), dz = fmaxf(fmaxf(a.z, -b.z), 0.0f);
+        *dmin = fmaxf(sqrtf(dx * dx + dy * dy + dz * dz) * 0.9999f - 1e-4f * R, 0.0f);
+        return true;
+    };
+    uint32_t stack[48];
+    int sp = 0;
+    stack[sp++] = V.S.tlas[0].wide_root;
+    uint2 best[TILE_LIST_CAP];
+    uint32_t cnt = 0;
+    bool overflow = false;
+    while (sp > 0 && !overflow)
+    {
+        const uint4* np = V.S.wide + (size_t)stack[--sp] * 5;
+        const uint4 q0 = PTB_LDG4U(np), q1 = PTB_LDG4U(np + 1), q2 = PTB_LDG4U(np + 2), q3 = PTB_LDG4U(np + 3), q4 = PTB_LDG4U(np + 4);
+        const V3 p = ex::v3(ex::from_bits(q0.x), ex::from_bits(q0.y), ex::from_bits(q0.z));
+        const V3 sc = ex::v3(ex::from_bits((q0.w & 0xffu) << 23), ex::from_bits(((q0.w >> 8) & 0xffu) << 23), ex::from_bits(((q0.w >> 16) & 0xffu) << 23));
+        const uint32_t imask = q0.w >> 24, lmask = q1.z & 0xffu;
+        const uint32_t lo_w[6] = {q2.x, q2.y, q2.z, q2.w, q3.x, q3.y}, hi_w[6] = {q3.z, q3.w, q4.x, q4.y, q4.z, q4.w};  // x, y, z planes of the slots 0-3 | 4-7
+        for (uint32_t s = 0; s < 8u; ++s)
+        {
+            if (!(((imask | lmask) >> s) & 1u)) continue;
+            float dmin;
+            if ((lmask >> s) & 1u)
+            {
+                const uint32_t hidx = q1.y + popc32(lmask & ((1u << s) - 1u));
+                const float4* lp = V.S.leaf_headers + (size_t)hidx * LEAF_F4;
+                const float4 h0 = PTB_LDG4F(lp), h1 = PTB_LDG4F(lp + 1);
+                if (!touches(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), &dmin)) continue;
+                if (cnt == TILE_LIST_CAP) { overflow = true; break; }
+                // insertion by distance, nearest first
+                uint32_t i = cnt++;
+                for (; i > 0 && ex::from_bits(best[i - 1].y) > dmin; --i) best[i] = best[i - 1];
+                best[i].x = hidx; best[i].y = ex::bits(dmin);
+            }
+            else
+            {
+                const uint32_t sh = (s & 3u) * 8u, w = s >> 2;
+                // quantised child box (a superset of the child's own), one more step of slack on either side
+                const V3 lo = ex::v3(p.x + ((float)((lo_w[0 + w] >> sh) & 0xffu) - 1.0f) * sc.x, p.y + ((float)((lo_w[2 + w] >> sh) & 0xffu) - 1.0f) * sc.y,
+                                     p.z + ((float)((lo_w[4 + w] >> sh) & 0xffu) - 1.0f) * sc.z);
+                const V3 hi = ex::v3(p.x + ((float)((hi_w[0 + w] >> sh) & 0xffu) + 1.0f) * sc.x, p.y + ((float)((hi_w[2 + w] >> sh) & 0xffu) + 1.0f) * sc.y,
+                                     p.z + ((float)((hi_w[4 + w] >> sh) & 0xffu) + 1.0f) * sc.z);
+                if (!touches(lo, hi, &dmin)) continue;
+                if (sp == 48) { overflow = true; break; }
+                stack[sp++] = q1.x + popc32(imask & ((1u << s) - 1u));
+            }
+        }
+    }
+    out[0].x = overflow ? TILE_LIST_NONE : cnt; out[0].y = 0u;
+    if (!overflow)
+        for (uint32_t i = 0; i < cnt; ++i) out[1 + i] = best[i];
+}
+
 // ---- regen ---------------------------------------------------------------------------------------------------------------
 // Finalises the slot's finished sample (if any), then starts the next one; the camera ray is returned in registers (and
 // stored) so the caller can trace it right away.

@@ -68,6 +68,23 @@ def trace_mr(es, o, d, tmax, which=0, any_hit=False, K=3, free_quorum=24, qn=16,
     return out
 
 
+TILE_LIST_STRIDE = 16
+
+
+def tile_lists(es, sd, W, H):
+    """tile_list_build (wavefront.h) for every 8 x 4 pixel tile of a W x H frame: (lists[n_tiles, 16, 2] uint32, slot -> pixel map,
+    instance -> TLAS leaf-header index)"""
+    m, eye = camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
+    n_tiles = (W // 8) * (H // 4)
+    lists = np.zeros((n_tiles, TILE_LIST_STRIDE, 2), np.uint32)
+    s2p = np.zeros(W * H, np.uint32)
+    lib().emu_tile_lists(C.c_void_p(es.h), _p(m), _p(eye), W, H, _p(lists), _p(s2p))
+    n_inst = len(sd.instances)
+    leaf = np.zeros(n_inst, np.uint32)
+    lib().emu_instance_leaf_headers(C.c_void_p(es.h), _p(leaf), n_inst)
+    return lists, s2p, leaf
+
+
 def camera(origin, target, fov_deg, aspect):
     m = np.zeros(16, np.float32)
     eye = np.zeros(3, np.float32)

@@ -325,3 +325,51 @@ extern "C" void emu_trace_mr(void* h, int which, int any, uint64_t n, const floa
         inst[i] = hit[i] ? gi[i] - S.tlas[which].inst_base : 0xffffffffu;
     }
 }
+
+// candidate lists of camera-ray tiles (tile_list_build, wavefront.h) for a W x H frame: lists = n_tiles * TILE_LIST_STRIDE uint2;
+// also the slot -> pixel map of the tiled layout for n slots of a layer
+extern "C" void emu_tile_lists(void* h, const float* cam_m16, const float* cam_eye3, uint32_t W, uint32_t H, uint32_t* lists2, uint32_t* slot_to_pixel)
+{
+    const HostScene& sc = *(HostScene*)h;
+    RenderView V{};
+    V.S = host_view(sc);
+    std::memcpy(V.cam.m, cam_m16, 64);
+    std::memcpy(V.cam.eye, cam_eye3, 12);
+    V.W = W; V.H = H; V.npix = W * H; V.K = 1;
+    V.tiles_x = W / 8u;
+    const uint32_t n_tiles = V.tiles_x * (H / 4u);
+    for (uint32_t t = 0; t < n_tiles; ++t) tile_list_build(V, t, reinterpret_cast<uint2*>(lists2) + (size_t)t * TILE_LIST_STRIDE);
+    for (uint32_t j = 0; j < V.npix; ++j) slot_to_pixel[j] = slot_pixel(V, j);
+}
+// the TLAS leaf (leaf-header index) of an instance row: what a tile list names
+extern "C" void emu_instance_leaf_headers(void* h, uint32_t* out, uint32_t n_inst)
+{
+    const HostScene& sc = *(HostScene*)h;
+    for (uint32_t i = 0; i < n_inst; ++i) out[i] = 0xffffffffu;
+    const uint32_t ib = sc.tlas[0].inst_base;
+    for (size_t k = 0; k < sc.leaf_headers.size(); ++k)
+    {
+        // TLAS-level headers carry the instance row in `first` and the inv_matrix in the payload; a BLAS-level header's `first` is a triangle
+        // slot, so identify TLAS leaves by walking the wide TLAS instead
+        (void)k;
+    }
+    const SceneDev S = host_view(sc);
+    std::vector<uint32_t> st{S.tlas[0].wide_root};
+    while (!st.empty())
+    {
+        const uint32_t node = st.back(); st.pop_back();
+        const uint4* np = S.wide + (size_t)node * 5;
+        const uint32_t imask = np[0].w >> 24, lmask = np[1].z & 0xffu;
+        for (uint32_t s8 = 0; s8 < 8; ++s8)
+        {
+            if ((imask >> s8) & 1u) st.push_back(np[1].x + (uint32_t)__builtin_popcount(imask & ((1u << s8) - 1u)));
+            if ((lmask >> s8) & 1u)
+            {
+                const uint32_t hidx = np[1].y + (uint32_t)__builtin_popcount(lmask & ((1u << s8) - 1u));
+                const float4* lp = S.leaf_headers + (size_t)hidx * LEAF_F4;
+                const uint32_t row = ex::bits(lp[1].w);
+                if (row >= ib && row - ib < n_inst) out[row - ib] = hidx;
+            }
+        }
+    }
+}

@@ -69,6 +69,45 @@ def test_multiray_stage_logic_matches_one_ray_traversal(po, scenes, emu, name):
                 assert np.array_equal(ga["hit"], ref_any["hit"]), (name, which, K, "any")
 
 
+@pytest.mark.parametrize("name,W,H", [("c3_small", 96, 56), ("c3_small", 32, 16), ("c4_small", 96, 56), ("c2", 64, 36), ("c1", 64, 36), ("materials", 64, 36)])
+def test_tile_lists_hold_every_instance_a_camera_ray_hits(po, scenes, emu, name, W, H):
+    """tile_list_build (wavefront.h, the body of k_tile_lists): the list of an 8 x 4 pixel tile must name every TLAS leaf a camera ray of
+    the tile can hit — rays through every pixel of the tile at random and at extreme sub-pixel jitter are traced the ordinary way, and the
+    instance each one hits has to be in its tile's list with a distance bound not beyond the hit; a tile with an empty list has no hit."""
+    sd = {"c1": scenes.scene_c1, "c2": scenes.scene_c2, "c3_small": lambda: scenes.scene_c3(grid=8), "materials": scenes.scene_materials_test,
+          "c4_small": lambda: scenes.scene_c4(nverts=150, n_spheres=8)}[name]()
+    es = emu.EmuScene(sd, po.pack_scene)
+    lists, s2p, leaf = emu.tile_lists(es, sd, W, H)
+    assert np.array_equal(np.sort(s2p), np.arange(W * H, dtype=np.uint32)), "the tiled slot layout is a bijection onto the pixels"
+    npix = W * H
+    pixel = s2p.astype(np.int64)
+    x, y = (pixel % W).astype(np.float32), (pixel // W).astype(np.float32)
+    tile = np.arange(npix) >> 5
+    rng = np.random.default_rng(7)
+    n_listed = 0
+    for jitter in ("random", "random", "lo", "hi", "mixed"):
+        if jitter == "random":
+            jx, jy = rng.random(npix, dtype=np.float32) - np.float32(0.5), rng.random(npix, dtype=np.float32) - np.float32(0.5)
+        else:
+            e = np.float32(0.49999997)
+            jx = np.full(npix, -0.5 if jitter == "lo" else e, np.float32)
+            jy = np.full(npix, -0.5 if jitter in ("lo", "mixed") else e, np.float32)
+        st = np.stack([(x + jx) / np.float32(W), (y + jy) / np.float32(H)], axis=1).astype(np.float32)  # main.rs:196-197 as regen_slot computes it
+        o, d = emu.camera_rays(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H), st)
+        r = es.trace(o, d, np.full(npix, np.inf, np.float32))
+        for j in np.nonzero(r["hit"])[0]:
+            row = lists[tile[j]]
+            n = int(row[0, 0])
+            if n == 0xffffffff:
+                continue  # more leaves than a list holds: such a tile walks the TLAS
+            want = leaf[r["inst"][j]]
+            k = np.nonzero(row[1:1 + n, 0] == want)[0]
+            assert k.size == 1, f"{name} {W}x{H}: tile {tile[j]} lacks the instance its ray (slot {j}, jitter {jitter}) hits"
+            assert row[1 + k[0], 1].view(np.float32) <= r["t"][j], "the entry-distance bound of a listed leaf lies beyond a hit inside it"
+            n_listed += 1
+    assert n_listed > 0 or name == "c2"
+
+
 def test_integer_tier_bit_exact(po, emu):
     idx = (np.arange(20000, dtype=np.uint32) * 7) % 5
     seeds = (np.arange(20000, dtype=np.uint32) * np.uint32(2654435761)).astype(np.uint32)
