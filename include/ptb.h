@@ -249,7 +249,9 @@ int ptb_get_launch_log(ptb_context* ctx, uint32_t capacity, int32_t* stage, floa
  *   tile_lists        camera rays start from their tile's list of TLAS leaves instead of the TLAS root: once per ptb_render one thread per
  *                     8 x 4 pixel tile walks the world TLAS with the tile's frustum and lists the instances its rays can reach, nearest
  *                     first (csrc/render.cu: k_tile_lists; needs tile_pixels).  1, 0, < 0 (default) = scenes of >= 64 instances.  Same
- *                     results but for equal hits in different instances (visit order).  tile_settle (0): 1 = a camera ray whose tile's list
+ *                     results but for equal hits in different instances (visit order).  tile_nodes (1): the walk goes on inside an
+ *                     instance while the frustum stays within one to three BLAS nodes; camera rays start their BLAS walk at those nodes
+ *                     (an instance whose BLAS the frustum misses is dropped from the list).  tile_settle (0): 1 = a camera ray whose tile's list
  *                     is empty is settled in the regeneration loop like one that cannot reach the scene bounds (counter [7]; same frame)
  *   nee_overlap       thin iterations (fewer live slots than this many per lane of the one-ray grid; 0 never = default, < 0 always): k_nee
  *                     of iteration i runs on a stream of its own beside the continuing slots' part of iteration i + 1's k_extend — a

@@ -92,6 +92,7 @@ struct ptb_context
     int opt_refill_below = -1, opt_nee_refill_below = 8;   // persistent kernels refill idle lanes when fewer than this many lanes of a warp are traversing
     int opt_shade_class = -1;     // k_shade_ordered instantiated for the scene's material kinds (-1, default) or the general body (0)
     int opt_multiray = -1;        // rays per lane of k_extend / k_nee: 0 = one (persist.cuh), 2 / 3 = multiray.cuh, -1 = by scene size (render.cu)
+    int opt_tile_nodes = 1;       // tile lists also name the one to three BLAS nodes a tile's frustum stays within: camera rays start their BLAS walk there
     int opt_tile_settle = 0;      // camera rays of tiles with an empty list are settled without a traversal (C4 -1.6 % per frame; off: they stay traced rays)
     int opt_tile_lists = -1;      // camera rays start from their tile's list of TLAS leaves (k_tile_lists): 1, 0, < 0 = scenes of >= 64 instances
     int opt_tile_pixels = 1;      // slots laid over the frame in 8 x 4 pixel tiles (a warp's 32 rays cover a compact patch) instead of row-major lines

@@ -433,6 +433,7 @@ int ptb_set_option(ptb_context* ctx, const char* name, int value)
     else if (n == "node_quorum") ctx->opt_node_quorum = value;
     else if (n == "shade_class") ctx->opt_shade_class = value;
     else if (n == "multiray") ctx->opt_multiray = (value == 2 || value == 3 || value < 0) ? value : 0;
+    else if (n == "tile_nodes") ctx->opt_tile_nodes = value ? 1 : 0;
     else if (n == "tile_settle") ctx->opt_tile_settle = value ? 1 : 0;
     else if (n == "tile_lists") ctx->opt_tile_lists = value;
     else if (n == "tile_pixels") ctx->opt_tile_pixels = value ? 1 : 0;

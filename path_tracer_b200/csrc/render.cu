@@ -1495,6 +1495,7 @@ int ptb_render(ptb_context* ctx, uint32_t sample_begin, uint32_t sample_count, u
         PTB_CUDA(ctx, rs.tile_lists.resize((size_t)n_tiles * TILE_LIST_STRIDE));
         V.S.tile_lists = rs.tile_lists.p;
         V.tile_settle = ctx->opt_tile_settle ? 1u : 0u;
+        V.tile_nodes = ctx->opt_tile_nodes ? 1u : 0u;
     }
     V.K = K;
     V.sample_begin = sample_begin; V.sample_count = sample_count;

@@ -217,6 +217,7 @@ PTB_HD void stk_set(const HybridStack<NS, STRIDE>& h, int i, uint2 v)
 }
 
 constexpr uint32_t TRAV_NONE = 0xffffffffu;
+constexpr uint32_t TILE_NODES_SHIFT_ = 28;  // tile-list instance entries: leaf-header index | number of node entries << 28 (wavefront.h)
 struct WideTrav
 {
     V3 ow, dw, invw;    // world-space ray and its exact inv_direction (ray.rs:1-8)
@@ -347,13 +348,16 @@ PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, Stack stack)
                 s.ray.oi = s.oiw;
             }
             uint2 e;
+            uint32_t list_nodes = 0u;  // LIST: BLAS nodes the tile's frustum stays within, listed after the instance's entry
             if (s.sp == 0)
             {
                 if (!LIST || s.cand >= s.cand_end) return false;
                 const uint2 c = S.tile_lists[s.cand++];
                 if (ex::from_bits(c.y) > s.t_max) { s.cand = s.cand_end; return false; }  // nearest first: nothing further can be nearer than the hit
-                e.x = c.x;
+                e.x = c.x & ((1u << TILE_NODES_SHIFT_) - 1u);
                 e.y = 0x80000000u;
+                list_nodes = c.x >> TILE_NODES_SHIFT_;
+                s.cand += list_nodes;  // the instance's node entries (read below when its box is hit)
             }
             else e = stk_get(stack, --s.sp);
             if (e.y & 0x80000000u)
@@ -373,7 +377,21 @@ PTB_HD bool wide_step_pop(WideTrav& s, const SceneDev& S, Stack stack)
                     const float inv12[12] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w, i2.x, i2.y, i2.z, i2.w};
                     transform_ray_reuse(s.ray, s.ow, s.dw, s.invw, inv12);
                     s.blas_sp = s.sp;
-                    if (cw & TLAS_DIRECT_FLAG)
+                    if (LIST && list_nodes)
+                    {
+                        // start below the BLAS root: the listed nodes as one-child groups, farthest first on the stack, the nearest at hand
+                        const uint32_t one = 1u | ((1u << s.ray.oi) << 8);  // descends to G.x: hit bit 0 -> slot oi, the only bit of the mask
+                        for (uint32_t q = list_nodes - 1u; q > 0u; --q)
+                        {
+                            uint2 g;
+                            g.x = S.tile_lists[s.cand - list_nodes + q].x;
+                            g.y = one;
+                            stk_set(stack, s.sp++, g);
+                        }
+                        s.G.x = S.tile_lists[s.cand - list_nodes].x;
+                        s.G.y = one;
+                    }
+                    else if (cw & TLAS_DIRECT_FLAG)
                     {
                         // a BLAS of one or two leaves: straight to the exact leaf tests (stage L of this very step)
                         s.lmask = (cw >> TLAS_DIRECT_BASE_BITS) & 0xffu;

@@ -58,6 +58,7 @@ struct RenderView
     uint32_t W, H;
     uint32_t npix;           // W * H
     uint32_t K;              // slots per pixel: slot = k * npix + j renders the samples k, k + K, k + 2K, ... of pixel slot_pixel(j)
+    uint32_t tile_nodes;     // tile lists also name the BLAS nodes a tile's frustum stays within (option tile_nodes)
     uint32_t tile_settle;    // camera rays of a tile whose list of TLAS leaves is empty are settled in the regeneration loop (option tile_settle)
     uint32_t tiles_x;        // > 0: slots are laid over the frame in tiles of 8 x 4 pixels (W / 8 tiles per row), so that the 32 rays of a warp
                              // cover a compact patch of the image instead of a 32 x 1 line; 0: j = pixel (frame sizes that do not divide)
@@ -110,9 +111,114 @@ PTB_HD float4 f4(float x, float y, float z, float w)
 
 // ---- candidate list of one 8 x 4 pixel tile (k_tile_lists, render.cu; host-callable so that the culling can be tested on the CPU) -------------
 // Walks the world TLAS with the tile's frustum — the four rays through the corners of its pixel area, jitter and a margin included — and
-// writes the TLAS leaves the frustum touches, nearest first, each with a lower bound of the distance at which a ray can enter it.
-// out: TILE_LIST_STRIDE entries, [0] = (count | TILE_LIST_NONE when the tile sees more leaves than the list holds, 0).
-constexpr uint32_t TILE_LIST_CAP = TILE_LIST_STRIDE - 1;
+// writes the TLAS leaves the frustum touches, nearest first, each with a lower bound of the distance at which a ray can enter it.  Inside
+// an instance the walk goes on in BLAS space while the frustum stays within one to three nodes: those nodes follow the instance's entry,
+// and a camera ray of the tile starts its BLAS walk there instead of at the BLAS root (an instance none of whose nodes the frustum
+// touches is dropped).
+// out: TILE_LIST_STRIDE entries, [0] = (number of entries that follow | TILE_LIST_NONE when the tile sees more than the list holds, 0);
+// an instance entry = (leaf-header index | k << TILE_NODES_SHIFT, distance bound), followed by its k node entries (wide node index, 0),
+// nearest first; k = 0: the BLAS root.
+constexpr uint32_t TILE_LIST_CAP = TILE_LIST_STRIDE - 1, TILE_NODES_SHIFT = 28, TILE_NODES_MAX = 3;
+struct TileFrustum
+{
+    V3 e;     // apex
+    V3 n[4];  // inward unit normals of the four side planes
+};
+PTB_HD TileFrustum tile_frustum(V3 e, const V3* c)  // c: the four corner directions in order around the tile
+{
+    TileFrustum F;
+    F.e = e;
+    for (int k = 0; k < 4; ++k)
+    {
+        V3 m = crossf(c[k], c[(k + 1) & 3]);
+        m = m * (1.0f / sqrtf(dot(m, m)));
+        if (dot(m, c[(k + 2) & 3]) < 0.0f) m = -m;
+        F.n[k] = m;
+    }
+    return F;
+}
+// false: every corner of the box lies outside one side plane (margin: 1e-4 of the box's distance scale).  *dmin: lower bound of the
+// distance from the apex to the box
+PTB_HD bool frustum_touches(const TileFrustum& F, V3 lo, V3 hi, float* dmin)
+{
+    const V3 a = lo - F.e, b = hi - F.e;
+    const float R = fmaxf(fmaxf(fmaxf(fabsf(a.x), fabsf(b.x)), fmaxf(fabsf(a.y), fabsf(b.y))), fmaxf(fabsf(a.z), fabsf(b.z)));
+    for (int k = 0; k < 4; ++k)
+    {
+        const float s = fmaxf(F.n[k].x * a.x, F.n[k].x * b.x) + fmaxf(F.n[k].y * a.y, F.n[k].y * b.y) + fmaxf(F.n[k].z * a.z, F.n[k].z * b.z);
+        if (s < -1e-4f * R) return false;
+    }
+    const float dx = fmaxf(fmaxf(a.x, -b.x), 0.0f), dy = fmaxf(fmaxf(a.y, -b.y), 0.0f), dz = fmaxf(fmaxf(a.z, -b.z), 0.0f);
+    *dmin = fmaxf(sqrtf(dx * dx + dy * dy + dz * dz) * 0.9999f - 1e-4f * R, 0.0f);
+    return true;
+}
+// one 8-wide node: its words, and the quantised box of child slot s (a superset of the child's own) with one more step of slack
+struct WideWords
+{
+    uint4 q0, q1, q2, q3, q4;
+};
+PTB_HD WideWords wide_words(const SceneDev& S, uint32_t node)
+{
+    const uint4* np = S.wide + (size_t)node * 5;
+    WideWords w;
+    w.q0 = PTB_LDG4U(np); w.q1 = PTB_LDG4U(np + 1); w.q2 = PTB_LDG4U(np + 2); w.q3 = PTB_LDG4U(np + 3); w.q4 = PTB_LDG4U(np + 4);
+    return w;
+}
+PTB_HD void wide_child_box(const WideWords& w, uint32_t s, V3* lo, V3* hi)
+{
+    const V3 p = ex::v3(ex::from_bits(w.q0.x), ex::from_bits(w.q0.y), ex::from_bits(w.q0.z));
+    const V3 sc = ex::v3(ex::from_bits((w.q0.w & 0xffu) << 23), ex::from_bits(((w.q0.w >> 8) & 0xffu) << 23), ex::from_bits(((w.q0.w >> 16) & 0xffu) << 23));
+    const uint32_t lo_w[6] = {w.q2.x, w.q2.y, w.q2.z, w.q2.w, w.q3.x, w.q3.y}, hi_w[6] = {w.q3.z, w.q3.w, w.q4.x, w.q4.y, w.q4.z, w.q4.w};  // x, y, z planes of the slots 0-3 | 4-7
+    const uint32_t sh = (s & 3u) * 8u, h = s >> 2;
+    *lo = ex::v3(p.x + ((float)((lo_w[0 + h] >> sh) & 0xffu) - 1.0f) * sc.x, p.y + ((float)((lo_w[2 + h] >> sh) & 0xffu) - 1.0f) * sc.y,
+                 p.z + ((float)((lo_w[4 + h] >> sh) & 0xffu) - 1.0f) * sc.z);
+    *hi = ex::v3(p.x + ((float)((hi_w[0 + h] >> sh) & 0xffu) + 1.0f) * sc.x, p.y + ((float)((hi_w[2 + h] >> sh) & 0xffu) + 1.0f) * sc.y,
+                 p.z + ((float)((hi_w[4 + h] >> sh) & 0xffu) + 1.0f) * sc.z);
+}
+// the frustum's walk inside one BLAS: from the root down while it stays within TILE_NODES_MAX nodes and touches no triangle leaf of the
+// node it would leave.  Returns the number of nodes (0: the frustum touches nothing in this BLAS; 1 with nodes[0] == root: no gain).
+PTB_HD uint32_t tile_blas_frontier(const SceneDev& S, const TileFrustum& F, uint32_t root, uint32_t* nodes, float* dist)
+{
+    uint32_t n = 1;
+    bool final_[TILE_NODES_MAX] = {false, false, false};
+    nodes[0] = root;
+    dist[0] = 0.0f;
+    for (int iter = 0; iter < 24 && n > 0; ++iter)
+    {
+        uint32_t i = 0;
+        while (i < n && final_[i]) ++i;
+        if (i == n) break;
+        const WideWords w = wide_words(S, nodes[i]);
+        const uint32_t imask = w.q0.w >> 24, lmask = w.q1.z & 0xffu;
+        uint32_t ch[8], nch = 0;
+        float cd[8];
+        bool leaf_touched = false;
+        for (uint32_t s = 0; s < 8u; ++s)
+        {
+            if (!(((imask | lmask) >> s) & 1u)) continue;
+            V3 lo, hi;
+            float d;
+            wide_child_box(w, s, &lo, &hi);
+            if (!frustum_touches(F, lo, hi, &d)) continue;
+            if ((lmask >> s) & 1u) { leaf_touched = true; break; }
+            ch[nch] = w.q1.x + popc32(imask & ((1u << s) - 1u));
+            cd[nch++] = d;
+        }
+        if (leaf_touched || n - 1u + nch > TILE_NODES_MAX) { final_[i] = true; continue; }
+        // replace node i by its touched inner children (none: the node drops out)
+        nodes[i] = nodes[n - 1]; dist[i] = dist[n - 1]; final_[i] = final_[n - 1];
+        --n;
+        for (uint32_t k = 0; k < nch; ++k) { nodes[n] = ch[k]; dist[n] = cd[k]; final_[n] = false; ++n; }
+    }
+    // nearest first
+    for (uint32_t a = 1; a < n; ++a)
+        for (uint32_t b = a; b > 0 && dist[b - 1] > dist[b]; --b)
+        {
+            const uint32_t tn = nodes[b]; nodes[b] = nodes[b - 1]; nodes[b - 1] = tn;
+            const float td = dist[b]; dist[b] = dist[b - 1]; dist[b - 1] = td;
+        }
+    return n;
+}
 PTB_HD void tile_list_build(const RenderView& V, uint32_t tile, uint2* out)
 {
     const float x0 = (float)((tile % V.tiles_x) * 8u), y0 = (float)((tile / V.tiles_x) * 4u);
@@ -123,77 +229,77 @@ PTB_HD void tile_list_build(const RenderView& V, uint32_t tile, uint2* out)
     camera_ray(V.cam, u1, v0, &e, &c[1]);
     camera_ray(V.cam, u1, v1, &e, &c[2]);
     camera_ray(V.cam, u0, v1, &e, &c[3]);
-    // side planes through the eye: normal = cross of two neighbouring corner rays, turned towards the opposite corner
-    V3 n[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-    {
-        V3 m = crossf(c[k], c[(k + 1) & 3]);
-        m = m * (1.0f / sqrtf(dot(m, m)));
-        if (dot(m, c[(k + 2) & 3]) < 0.0f) m = -m;
-        n[k] = m;
-    }
-    // 1: the box may hold a point of the frustum; *dmin: lower bound of the distance from the eye to the box
-    auto touches = [&](V3 lo, V3 hi, float* dmin) -> bool {
-        const V3 a = lo - e, b = hi - e;
-        const float R = fmaxf(fmaxf(fmaxf(fabsf(a.x), fabsf(b.x)), fmaxf(fabsf(a.y), fabsf(b.y))), fmaxf(fabsf(a.z), fabsf(b.z)));
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-        {
-            const float s = fmaxf(n[k].x * a.x, n[k].x * b.x) + fmaxf(n[k].y * a.y, n[k].y * b.y) + fmaxf(n[k].z * a.z, n[k].z * b.z);
-            if (s < -1e-4f * R) return false;  // every corner of the box is outside this side plane
-        }
-        const float dx = fmaxf(fmaxf(a.x, -b.x), 0.0f), dy = fmaxf(fmaxf(a.y, -b.y), 0.0f), dz = fmaxf(fmaxf(a.z, -b.z), 0.0f);
-        *dmin = fmaxf(sqrtf(dx * dx + dy * dy + dz * dz) * 0.9999f - 1e-4f * R, 0.0f);
-        return true;
-    };
+    const TileFrustum F = tile_frustum(e, c);
+    // (1) the TLAS leaves the frustum touches, nearest first
+    constexpr uint32_t INST_CAP = 12;
     uint32_t stack[48];
     int sp = 0;
     stack[sp++] = V.S.tlas[0].wide_root;
-    uint2 best[TILE_LIST_CAP];
+    uint2 best[INST_CAP];
     uint32_t cnt = 0;
     bool overflow = false;
     while (sp > 0 && !overflow)
     {
-        const uint4* np = V.S.wide + (size_t)stack[--sp] * 5;
-        const uint4 q0 = PTB_LDG4U(np), q1 = PTB_LDG4U(np + 1), q2 = PTB_LDG4U(np + 2), q3 = PTB_LDG4U(np + 3), q4 = PTB_LDG4U(np + 4);
-        const V3 p = ex::v3(ex::from_bits(q0.x), ex::from_bits(q0.y), ex::from_bits(q0.z));
-        const V3 sc = ex::v3(ex::from_bits((q0.w & 0xffu) << 23), ex::from_bits(((q0.w >> 8) & 0xffu) << 23), ex::from_bits(((q0.w >> 16) & 0xffu) << 23));
-        const uint32_t imask = q0.w >> 24, lmask = q1.z & 0xffu;
-        const uint32_t lo_w[6] = {q2.x, q2.y, q2.z, q2.w, q3.x, q3.y}, hi_w[6] = {q3.z, q3.w, q4.x, q4.y, q4.z, q4.w};  // x, y, z planes of the slots 0-3 | 4-7
+        const WideWords w = wide_words(V.S, stack[--sp]);
+        const uint32_t imask = w.q0.w >> 24, lmask = w.q1.z & 0xffu;
         for (uint32_t s = 0; s < 8u; ++s)
         {
             if (!(((imask | lmask) >> s) & 1u)) continue;
             float dmin;
             if ((lmask >> s) & 1u)
             {
-                const uint32_t hidx = q1.y + popc32(lmask & ((1u << s) - 1u));
+                const uint32_t hidx = w.q1.y + popc32(lmask & ((1u << s) - 1u));
                 const float4* lp = V.S.leaf_headers + (size_t)hidx * LEAF_F4;
                 const float4 h0 = PTB_LDG4F(lp), h1 = PTB_LDG4F(lp + 1);
-                if (!touches(ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), &dmin)) continue;
-                if (cnt == TILE_LIST_CAP) { overflow = true; break; }
-                // insertion by distance, nearest first
+                if (!frustum_touches(F, ex::v3(h0.x, h0.y, h0.z), ex::v3(h1.x, h1.y, h1.z), &dmin)) continue;
+                if (cnt == INST_CAP) { overflow = true; break; }
                 uint32_t i = cnt++;
                 for (; i > 0 && ex::from_bits(best[i - 1].y) > dmin; --i) best[i] = best[i - 1];
                 best[i].x = hidx; best[i].y = ex::bits(dmin);
             }
             else
             {
-                const uint32_t sh = (s & 3u) * 8u, w = s >> 2;
-                // quantised child box (a superset of the child's own), one more step of slack on either side
-                const V3 lo = ex::v3(p.x + ((float)((lo_w[0 + w] >> sh) & 0xffu) - 1.0f) * sc.x, p.y + ((float)((lo_w[2 + w] >> sh) & 0xffu) - 1.0f) * sc.y,
-                                     p.z + ((float)((lo_w[4 + w] >> sh) & 0xffu) - 1.0f) * sc.z);
-                const V3 hi = ex::v3(p.x + ((float)((hi_w[0 + w] >> sh) & 0xffu) + 1.0f) * sc.x, p.y + ((float)((hi_w[2 + w] >> sh) & 0xffu) + 1.0f) * sc.y,
-                                     p.z + ((float)((hi_w[4 + w] >> sh) & 0xffu) + 1.0f) * sc.z);
-                if (!touches(lo, hi, &dmin)) continue;
+                V3 lo, hi;
+                wide_child_box(w, s, &lo, &hi);
+                if (!frustum_touches(F, lo, hi, &dmin)) continue;
                 if (sp == 48) { overflow = true; break; }
-                stack[sp++] = q1.x + popc32(imask & ((1u << s) - 1u));
+                stack[sp++] = w.q1.x + popc32(imask & ((1u << s) - 1u));
             }
         }
     }
-    out[0].x = overflow ? TILE_LIST_NONE : cnt; out[0].y = 0u;
-    if (!overflow)
-        for (uint32_t i = 0; i < cnt; ++i) out[1 + i] = best[i];
+    if (overflow) { out[0].x = TILE_LIST_NONE; out[0].y = 0u; return; }
+    // (2) inside each instance: the frustum in BLAS space (Ray::transform's map applied to the apex and the corner directions)
+    uint32_t n_out = 0;
+    for (uint32_t i = 0; i < cnt; ++i)
+    {
+        const float4* lp = V.S.leaf_headers + (size_t)best[i].x * LEAF_F4;
+        const uint32_t cw = ex::bits(PTB_LDG4F(lp).w);
+        uint32_t nodes[TILE_NODES_MAX], k = 0;
+        if (V.tile_nodes && !(cw & TLAS_DIRECT_FLAG))
+        {
+            const float4 i0 = PTB_LDG4F(lp + 2), i1 = PTB_LDG4F(lp + 3), i2 = PTB_LDG4F(lp + 4);
+            const M3 A{ex::v3(i0.x, i0.y, i0.z), ex::v3(i0.w, i1.x, i1.y), ex::v3(i1.z, i1.w, i2.x)};
+            const V3 t = ex::v3(i2.y, i2.z, i2.w);
+            V3 cb[4];
+            for (int q = 0; q < 4; ++q) cb[q] = mulm(A, c[q]);
+            const TileFrustum FB = tile_frustum(mulm(A, e) + t, cb);
+            float dist[TILE_NODES_MAX];
+            k = tile_blas_frontier(V.S, FB, cw, nodes, dist);
+            if (k == 0u) continue;                    // the frustum touches nothing inside: not a candidate
+            if (k == 1u && nodes[0] == cw) k = 0u;    // still the root
+        }
+        if (n_out + 1u + k > TILE_LIST_CAP)
+        {
+            if (n_out + 1u > TILE_LIST_CAP) { out[0].x = TILE_LIST_NONE; out[0].y = 0u; return; }
+            k = 0u;  // no room for its nodes: from the BLAS root
+        }
+        out[1u + n_out].x = best[i].x | (k << TILE_NODES_SHIFT);
+        out[1u + n_out].y = best[i].y;
+        ++n_out;
+        for (uint32_t q = 0; q < k; ++q) { out[1u + n_out].x = nodes[q]; out[1u + n_out].y = 0u; ++n_out; }
+    }
+    out[0].x = n_out;
+    out[0].y = 0u;
 }
 
 // ---- regen ---------------------------------------------------------------------------------------------------------------

@@ -85,6 +85,16 @@ def tile_lists(es, sd, W, H):
     return lists, s2p, leaf
 
 
+def trace_list(es, lists, tile_of, o, d):
+    """closest hit of camera rays from their tile's list (wide_begin_list, traverse.h), ray i in tile tile_of[i]"""
+    n = o.shape[0]
+    o, d = (np.ascontiguousarray(x, np.float32) for x in (o, d))
+    tile_of = np.ascontiguousarray(tile_of, np.uint32)
+    out = dict(hit=np.zeros(n, np.uint8), t=np.zeros(n, np.float32), u=np.zeros(n, np.float32), v=np.zeros(n, np.float32), prim=np.zeros(n, np.uint32), inst=np.zeros(n, np.uint32))
+    lib().emu_trace_list(C.c_void_p(es.h), _p(lists), C.c_uint64(n), _p(tile_of), _p(o), _p(d), _p(out["hit"]), _p(out["t"]), _p(out["u"]), _p(out["v"]), _p(out["prim"]), _p(out["inst"]))
+    return out
+
+
 def camera(origin, target, fov_deg, aspect):
     m = np.zeros(16, np.float32)
     eye = np.zeros(3, np.float32)

@@ -337,6 +337,7 @@ extern "C" void emu_tile_lists(void* h, const float* cam_m16, const float* cam_e
     std::memcpy(V.cam.eye, cam_eye3, 12);
     V.W = W; V.H = H; V.npix = W * H; V.K = 1;
     V.tiles_x = W / 8u;
+    V.tile_nodes = 1u;
     const uint32_t n_tiles = V.tiles_x * (H / 4u);
     for (uint32_t t = 0; t < n_tiles; ++t) tile_list_build(V, t, reinterpret_cast<uint2*>(lists2) + (size_t)t * TILE_LIST_STRIDE);
     for (uint32_t j = 0; j < V.npix; ++j) slot_to_pixel[j] = slot_pixel(V, j);
@@ -371,5 +372,31 @@ extern "C" void emu_instance_leaf_headers(void* h, uint32_t* out, uint32_t n_ins
                 if (row >= ib && row - ib < n_inst) out[row - ib] = hidx;
             }
         }
+    }
+}
+
+// closest hit of camera rays that start from their tile's list (wide_begin_list + wide_step_pop<true>), ray i belonging to tile tile_of[i]
+extern "C" void emu_trace_list(void* h, const uint32_t* lists2, uint64_t n, const uint32_t* tile_of, const float* o, const float* d, uint8_t* hit, float* t, float* u, float* v,
+                               uint32_t* prim, uint32_t* inst)
+{
+    const HostScene& sc = *(HostScene*)h;
+    SceneDev S = host_view(sc);
+    S.tile_lists = reinterpret_cast<const uint2*>(lists2);
+    for (uint64_t i = 0; i < n; ++i)
+    {
+        const V3 ro = ex::v3(o[i * 3], o[i * 3 + 1], o[i * 3 + 2]), rd = ex::v3(d[i * 3], d[i * 3 + 1], d[i * 3 + 2]);
+        uint2 stack[WIDE_STACK_CAP];
+        WideTrav s;
+        const uint32_t first = tile_of[i] * TILE_LIST_STRIDE, cnt = S.tile_lists[first].x;
+        if (cnt == TILE_LIST_NONE) wide_begin(s, S, 0, ro, rd, ex::inf(), false);
+        else wide_begin_list(s, S, ro, rd, ex::inf(), first + 1u, first + 1u + cnt);
+        while (wide_step_pop<true>(s, S, stack) && wide_step_work<0>(s, S, stack, true)) {}
+        const bool f = s.hit_inst != TRAV_NONE;
+        hit[i] = f;
+        t[i] = f ? s.t_max : ex::inf();
+        u[i] = f ? wide_hit_u(s) : 0.0f;
+        v[i] = f ? wide_hit_v(s) : 0.0f;
+        prim[i] = f ? S.tri_prim[s.hit_slot] : 0xffffffffu;
+        inst[i] = f ? s.hit_inst - S.tlas[0].inst_base : 0xffffffffu;
     }
 }

@@ -419,11 +419,12 @@ def test_tile_lists_equal_tlas_walk(ptb, scenes, name, spp, W, H):
     (tile_pixels = 0: no lists)."""
     sd = _scene(scenes, name)
     out = {}
-    for tl, tp in ((0, 1), (1, 1), (1, 0), (2, 1)):
+    for tl, tp in ((0, 1), (1, 1), (1, 0), (2, 1), (3, 1)):
         ctx = ptb.Context(0)
         ctx.upload(sd)
         ctx.set_option("tile_lists", min(tl, 1))
         ctx.set_option("tile_settle", 1 if tl == 2 else 0)
+        ctx.set_option("tile_nodes", 0 if tl == 3 else 1)
         ctx.set_option("tile_pixels", tp)
         ctx.set_camera(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H))
         ctx.frame_begin(W, H)

@@ -95,15 +95,31 @@ def test_tile_lists_hold_every_instance_a_camera_ray_hits(po, scenes, emu, name,
         st = np.stack([(x + jx) / np.float32(W), (y + jy) / np.float32(H)], axis=1).astype(np.float32)  # main.rs:196-197 as regen_slot computes it
         o, d = emu.camera_rays(sd.cam_origin, sd.cam_target, sd.fov_deg, np.float32(W) / np.float32(H), st)
         r = es.trace(o, d, np.full(npix, np.inf, np.float32))
+        # (a) the traversal that starts from the lists finds what the TLAS walk finds, bit for bit
+        g = emu.trace_list(es, lists, tile, o, d)
+        assert np.array_equal(g["hit"], r["hit"]), f"{name} {W}x{H} jitter {jitter}: hit / miss differs"
+        m = r["hit"] > 0
+        for key in ("prim", "inst"):
+            assert np.array_equal(g[key][m], r[key][m]), (name, W, H, jitter, key)
+        for key in ("t", "u", "v"):
+            assert np.array_equal(bits(g[key][m]), bits(r[key][m])), (name, W, H, jitter, key)
+        # (b) the lists themselves: the instance a ray hits is named, with a distance bound not beyond the hit
         for j in np.nonzero(r["hit"])[0]:
             row = lists[tile[j]]
             n = int(row[0, 0])
             if n == 0xffffffff:
-                continue  # more leaves than a list holds: such a tile walks the TLAS
+                continue  # more than a list holds: such a tile walks the TLAS
+            entries = row[1:1 + n]
+            is_inst = np.ones(n, bool)  # instance entries are followed by their k node entries
+            i = 0
+            while i < n:
+                k = int(entries[i, 0] >> 28)
+                is_inst[i + 1:i + 1 + k] = False
+                i += 1 + k
             want = leaf[r["inst"][j]]
-            k = np.nonzero(row[1:1 + n, 0] == want)[0]
+            k = np.nonzero(is_inst & ((entries[:, 0] & 0x0fffffff) == want))[0]
             assert k.size == 1, f"{name} {W}x{H}: tile {tile[j]} lacks the instance its ray (slot {j}, jitter {jitter}) hits"
-            assert row[1 + k[0], 1].view(np.float32) <= r["t"][j], "the entry-distance bound of a listed leaf lies beyond a hit inside it"
+            assert entries[k[0], 1].view(np.float32) <= r["t"][j], "the entry-distance bound of a listed leaf lies beyond a hit inside it"
             n_listed += 1
     assert n_listed > 0 or name == "c2"
 
