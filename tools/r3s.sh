@@ -1,4 +1,4 @@
-T=r3s
+T=r3w
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${T}_pytest.log
 tail -3 gpurun_out/${T}_pytest.log
