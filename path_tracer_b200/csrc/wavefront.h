@@ -180,7 +180,7 @@ PTB_HD void wide_child_box(const WideWords& w, uint32_t s, V3* lo, V3* hi)
 PTB_HD uint32_t tile_blas_frontier(const SceneDev& S, const TileFrustum& F, uint32_t root, uint32_t* nodes, float* dist)
 {
     uint32_t n = 1;
-    bool final_[TILE_NODES_MAX] = {false, false, false};
+    bool final_[TILE_NODES_MAX] = {};
     nodes[0] = root;
     dist[0] = 0.0f;
     for (int iter = 0; iter < 24 && n > 0; ++iter)
